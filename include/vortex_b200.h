@@ -1,0 +1,186 @@
+/* vortex_b200.h — C ABI of libvortex-b200.so, the B200 runtime backend for the Vortex ray-tracing path.
+ *
+ * Plain C: pointers, sizes and integers only.  Three groups of entry points:
+ *
+ *  (1) vx_dev_init()  — the ONE symbol the reference's stub dispatcher binds
+ *      (reference: runtime/common/callbacks.h:74, looked up by runtime/stub/vortex.cpp:58-97 after
+ *      dlopen("libvortex-$VORTEX_DRIVER.so")).  It fills the 16-slot callback table below, whose slot
+ *      order and signatures are the reference's callbacks_t (runtime/common/callbacks.h:23-72).
+ *      With VORTEX_DRIVER=b200 an unmodified Vortex host application runs on this backend.
+ *
+ *  (2) vx_* — the same 17 runtime calls + 4 upload helpers the reference declares in
+ *      runtime/include/vortex.h:80-145, exported directly so a host can also link this library
+ *      in place of the stub (no dlopen hop).  Names, argument meaning and error behaviour follow
+ *      the reference glue (runtime/common/callbacks.inc:20-225, runtime/stub/utils.cpp:25-122):
+ *      0 = success, non-zero (-1) = failure, null handles / zero sizes / out-of-range offsets rejected.
+ *
+ *  (3) vx_b200_* — extensions that have no reference counterpart (multi-GPU partition, device
+ *      pointer export for NCCL, timing, per-ray hit-record queries, statistics).
+ *
+ * What vx_start() does here: it reads the kernel_arg_t bytes the host uploaded into the arguments
+ * buffer, ignores the RISC-V kernel image, and launches hand-written sm_100a CUDA kernels that
+ * consume the reference's scene buffers byte for byte:
+ *   - 192-byte kernel_arg_t  -> layout A, the software ray-caster (tests/regression/raycast/common.h:120-147)
+ *   - 216-byte kernel_arg_t  -> layout B, the simx RT-unit path   (tests/regression/raytracing/common.h:164-195)
+ * There is no CPU fallback: every entry point fails (non-zero) when no CUDA device is usable.
+ */
+#ifndef VORTEX_B200_H
+#define VORTEX_B200_H
+
+#include <stdint.h>
+#include <stdio.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void *vx_device_h;
+typedef void *vx_buffer_h;
+
+/* ---- capability ids (reference: runtime/include/vortex.h:30-44) ---- */
+#define VX_CAPS_VERSION 0x0
+#define VX_CAPS_NUM_THREADS 0x1
+#define VX_CAPS_NUM_WARPS 0x2
+#define VX_CAPS_NUM_CORES 0x3
+#define VX_CAPS_CACHE_LINE_SIZE 0x4
+#define VX_CAPS_GLOBAL_MEM_SIZE 0x5
+#define VX_CAPS_LOCAL_MEM_SIZE 0x6
+#define VX_CAPS_ISA_FLAGS 0x7
+#define VX_CAPS_NUM_MEM_BANKS 0x8
+#define VX_CAPS_MEM_BANK_SIZE 0x9
+#define VX_CAPS_NUM_CLUSTERS 0xA
+#define VX_CAPS_SOCKET_SIZE 0xB
+#define VX_CAPS_ISSUE_WIDTH 0xC
+#define VX_CAPS_CLOCK_RATE 0xD
+#define VX_CAPS_PEAK_MEM_BW 0xE
+
+/* ---- memory access flags (reference: vortex.h:74-78) ---- */
+#define VX_MEM_READ 0x1
+#define VX_MEM_WRITE 0x2
+#define VX_MEM_READ_WRITE 0x3
+#define VX_MEM_PIN_MEMORY 0x4
+
+#define VX_MAX_TIMEOUT (24 * 60 * 60 * 1000)
+
+/* ---- device configuration registers this backend understands (reference: hw/VX_types.toml:16-19,
+ *      generated VX_types.h: VX_DCR_BASE_*).  0x006..0x009 carry the RT-unit scene pointers the
+ *      raytracing host writes (tests/regression/raytracing/tracer.cpp:252-256). ---- */
+#define VX_DCR_BASE_STARTUP_ADDR0 0x001
+#define VX_DCR_BASE_STARTUP_ADDR1 0x002
+#define VX_DCR_BASE_STARTUP_ARG0 0x003
+#define VX_DCR_BASE_STARTUP_ARG1 0x004
+#define VX_DCR_BASE_MPM_CLASS 0x005
+#define VX_DCR_BASE_RTX_TLAS_PTR 0x006
+#define VX_DCR_BASE_RTX_BLAS_PTR 0x007
+#define VX_DCR_BASE_RTX_BVH_PTR 0x008
+#define VX_DCR_BASE_RTX_TRI_PTR 0x009
+/* b200-private DCRs (outside every range the reference assigns: base 0x001-0x00A, DXA 0x100-0x280) */
+#define VX_DCR_B200_RT_MODE 0x0F0    /* bit0 shadow rays, bit1 diffuse bounces (SURVEY 8d extensions); default 0 */
+#define VX_DCR_B200_RT_LAYOUT 0x0F1  /* 0 = infer from argument size (192 -> A, 216 -> B), 1 = A, 2 = B */
+#define VX_DCR_B200_RT_ORDER 0x0F2   /* 0 = near-first BLAS order (fast), 1 = the reference's far-first order (strict) */
+
+#define VX_B200_MODE_SHADOW 0x1u
+#define VX_B200_MODE_DIFFUSE 0x2u
+
+/* ---- performance counter addresses answered by vx_mpm_query (reference: VX_types.h VX_CSR_*) ---- */
+#define VX_CSR_MPM_BASE 0xB00
+#define VX_CSR_MCYCLE 0xB00
+#define VX_CSR_MINSTRET 0xB02
+
+/* ---- (1) the dispatcher hook ------------------------------------------------------------------ */
+typedef struct {
+  int (*dev_open)(vx_device_h *hdevice);
+  int (*dev_close)(vx_device_h hdevice);
+  int (*dev_caps)(vx_device_h hdevice, uint32_t caps_id, uint64_t *value);
+  int (*mem_alloc)(vx_device_h hdevice, uint64_t size, int flags, vx_buffer_h *hbuffer);
+  int (*mem_reserve)(vx_device_h hdevice, uint64_t address, uint64_t size, int flags, vx_buffer_h *hbuffer);
+  int (*mem_free)(vx_buffer_h hbuffer);
+  int (*mem_access)(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, int flags);
+  int (*mem_address)(vx_buffer_h hbuffer, uint64_t *address);
+  int (*mem_info)(vx_device_h hdevice, uint64_t *mem_free, uint64_t *mem_used);
+  int (*copy_to_dev)(vx_buffer_h hbuffer, const void *host_ptr, uint64_t dst_offset, uint64_t size);
+  int (*copy_from_dev)(void *host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, uint64_t size);
+  int (*start)(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments);
+  int (*ready_wait)(vx_device_h hdevice, uint64_t timeout);
+  int (*dcr_read)(vx_device_h hdevice, uint32_t addr, uint32_t *value);
+  int (*dcr_write)(vx_device_h hdevice, uint32_t addr, uint32_t value);
+  int (*mpm_query)(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t *value);
+} callbacks_t; /* reference: runtime/common/callbacks.h:23-72 — same slot order */
+
+int vx_dev_init(callbacks_t *callbacks); /* reference: runtime/common/callbacks.h:74 */
+
+/* ---- (2) the runtime API, exported directly (reference: runtime/include/vortex.h:80-145) -------- */
+int vx_dev_open(vx_device_h *hdevice);                                    /* vortex.h:81  */
+int vx_dev_close(vx_device_h hdevice);                                    /* vortex.h:84  */
+int vx_dev_caps(vx_device_h hdevice, uint32_t caps_id, uint64_t *value);  /* vortex.h:87  */
+int vx_mem_alloc(vx_device_h hdevice, uint64_t size, int flags, vx_buffer_h *hbuffer);                    /* vortex.h:90  */
+int vx_mem_reserve(vx_device_h hdevice, uint64_t address, uint64_t size, int flags, vx_buffer_h *hbuffer); /* vortex.h:93  */
+int vx_mem_free(vx_buffer_h hbuffer);                                     /* vortex.h:96  */
+int vx_mem_access(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, int flags);                         /* vortex.h:99  */
+int vx_mem_address(vx_buffer_h hbuffer, uint64_t *address);               /* vortex.h:102 */
+int vx_mem_info(vx_device_h hdevice, uint64_t *mem_free, uint64_t *mem_used);                              /* vortex.h:105 */
+int vx_copy_to_dev(vx_buffer_h hbuffer, const void *host_ptr, uint64_t dst_offset, uint64_t size);         /* vortex.h:108 */
+int vx_copy_from_dev(void *host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, uint64_t size);             /* vortex.h:111 */
+int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments);                            /* vortex.h:114 */
+int vx_ready_wait(vx_device_h hdevice, uint64_t timeout);                 /* vortex.h:117 */
+int vx_dcr_read(vx_device_h hdevice, uint32_t addr, uint32_t *value);     /* vortex.h:120 */
+int vx_dcr_write(vx_device_h hdevice, uint32_t addr, uint32_t value);     /* vortex.h:123 */
+int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t *value);                   /* vortex.h:126 */
+int vx_upload_kernel_bytes(vx_device_h hdevice, const void *content, uint64_t size, vx_buffer_h *hbuffer); /* vortex.h:131, stub/utils.cpp:25-61 */
+int vx_upload_kernel_file(vx_device_h hdevice, const char *filename, vx_buffer_h *hbuffer);                /* vortex.h:134 */
+int vx_upload_bytes(vx_device_h hdevice, const void *content, uint64_t size, vx_buffer_h *hbuffer);        /* vortex.h:137, stub/utils.cpp:88-106 */
+int vx_upload_file(vx_device_h hdevice, const char *filename, vx_buffer_h *hbuffer);                       /* vortex.h:140 */
+int vx_dump_perf(vx_device_h hdevice, FILE *stream);                                                       /* vortex.h:146 */
+
+/* ---- (3) b200 extensions ----------------------------------------------------------------------- */
+
+/* Which CUDA device the NEXT vx_dev_open() binds (default: env VORTEX_B200_DEVICE, else LOCAL_RANK, else 0). */
+int vx_b200_select_device(int cuda_device);
+
+/* Screen-space partition for multi-GPU runs: the image is cut into bands of `band_rows` rows and this
+ * device renders band j iff j % world == rank.  Pixels of other bands are left untouched.
+ * world == 1 (default) renders everything.  Env defaults: VORTEX_B200_RANK / VORTEX_B200_WORLD. */
+int vx_b200_set_partition(vx_device_h hdevice, uint32_t rank, uint32_t world, uint32_t band_rows);
+
+/* Raw CUDA device pointer behind a Vortex buffer (for NCCL / torch interop on the same process). */
+int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr);
+
+/* The CUDA stream (cudaStream_t as integer) all of this device's kernels and copies are issued on. */
+int vx_b200_stream(vx_device_h hdevice, uint64_t *cuda_stream);
+
+/* Device time of the kernels of the last completed vx_start()/vx_b200_trace_* (CUDA events on the launch stream). */
+int vx_b200_last_kernel_ms(vx_device_h hdevice, float *ms);
+
+typedef struct {
+  uint64_t rays;            /* TLASIntersect-equivalent queries issued by the last run (primary + bounce + shadow) */
+  uint64_t box_tests;       /* child boxes slab-tested   (only when statistics are enabled) */
+  uint64_t tri_tests;       /* triangles Moller-Trumbore tested */
+  uint64_t blas_entered;    /* instance (BLAS) entries */
+  uint64_t shaded_hits;     /* closest-hit shading invocations */
+  uint64_t kernel_launches; /* CUDA kernels launched by the last run */
+  uint64_t prep_launches;   /* of those: scene re-flatten kernels (0 when the cached GPU layout was reused) */
+  float kernel_ms;          /* == vx_b200_last_kernel_ms */
+  float prep_ms;            /* device time of the re-flatten pass inside the last run */
+} vx_b200_stats_t;
+
+/* Statistics of the last completed run.  Work counters other than `rays` are gathered only after
+ * vx_b200_enable_stats(dev, 1) (the counting kernels are slower; never enable it while timing). */
+int vx_b200_enable_stats(vx_device_h hdevice, int enable);
+int vx_b200_get_stats(vx_device_h hdevice, vx_b200_stats_t *stats);
+
+/* Closest-hit records instead of colours.  `harguments` holds a kernel_arg_t exactly as for vx_start.
+ *  - trace_primary: one ray per pixel (GenerateRay), hits[y*W+x]
+ *  - trace_rays   : `count` caller-supplied rays (6 floats each: origin, direction) read from hrays
+ * Each hit is the reference's 24-byte ray_hit_t {dist, bx, by, bz, blasIdx, triIdx}
+ * (tests/regression/raycast/common.h:24-29); misses keep dist = 1e30.  Asynchronous like vx_start:
+ * follow with vx_ready_wait. */
+int vx_b200_trace_primary(vx_device_h hdevice, vx_buffer_h harguments, vx_buffer_h hhits);
+int vx_b200_trace_rays(vx_device_h hdevice, vx_buffer_h harguments, vx_buffer_h hrays, uint64_t count, vx_buffer_h hhits);
+
+/* Human-readable description of the last error on this thread ("" if none). */
+const char *vx_b200_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VORTEX_B200_H */

@@ -1,0 +1,57 @@
+// rt_raycast.h — host-side launch interface of the layout-A (software ray-caster) CUDA path.
+#pragma once
+#include <cuda_runtime.h>
+#include "rt_layouts.h"
+
+namespace vxb {
+
+// Device pointers of one uploaded layout-A scene (already translated from Vortex addresses).
+struct SceneA {
+  const uint8_t *nodes;     // BvhNodeA[]  — consumed in place (a node pair is one 64-byte, 32-byte-aligned record)
+  const GpuTri *gtri;       // one per triIdx slot (built by launch_gather_tris)
+  const TlasNodeA *tlas;
+  const BlasNodeA *blas;
+  const TriExA *triEx;
+  const uint8_t *tex;
+  uint32_t tlas_root;
+};
+
+struct Partition {
+  uint32_t rank = 0, world = 1, band_rows = 8;
+};
+
+struct WorkCounters {       // device-resident, zeroed before each run
+  unsigned long long rays, box_tests, tri_tests, blas_entered, shaded_hits;
+};
+
+struct RenderA {
+  SceneA scene;
+  KernelArgA arg;           // camera, lights, spp, depth, dimensions (addresses inside are NOT used by the kernel)
+  uint32_t *out;            // framebuffer W*H
+  Partition part;
+  uint32_t mode;            // VX_B200_MODE_* bits
+  uint32_t strict_order;    // 1 = reference far-first BLAS order, no re-cull at pop
+  WorkCounters *counters;
+  uint32_t *tile_counter;   // device word, zeroed before each launch
+  int stats;                // gather box/tri/blas counters
+};
+
+struct TraceA {
+  SceneA scene;
+  KernelArgA arg;
+  const float *rays;        // 6 floats per ray, or nullptr => primary rays of `arg`
+  uint64_t count;
+  HitA *hits;
+  uint32_t strict_order;
+  WorkCounters *counters;
+  int stats;
+};
+
+// gtri[p] = triangle triIdx[p] in edge form, p in [0, n_slots).  Slots whose index is >= n_tris get a degenerate triangle.
+cudaError_t launch_gather_tris(const TriA *tri, const uint32_t *triIdx, GpuTri *gtri, uint64_t n_slots, uint64_t n_tris,
+                               cudaStream_t stream);
+// returns the number of kernels launched (>0) or a negative cudaError_t
+int launch_render_a(const RenderA &p, int num_sms, cudaStream_t stream);
+int launch_trace_a(const TraceA &p, int num_sms, cudaStream_t stream);
+
+}  // namespace vxb

@@ -1,0 +1,799 @@
+// vx_b200.cu — the b200 runtime backend: a vx_device over one B200, and the C ABI of include/vortex_b200.h.
+//
+// Mirrors the role of runtime/simx/vortex.cpp (class vx_device, :49-636) + runtime/common/callbacks.inc
+// (the handle/glue layer, :14-225) + runtime/stub/utils.cpp (upload helpers, :25-122) of the reference,
+// re-designed for CUDA: one arena allocation backs the Vortex address space, uploads/downloads are stream
+// ordered copies, vx_start decodes kernel_arg_t and launches the sm_100a ray-tracing kernels, vx_ready_wait
+// is a stream wait.  There is no simulator and no CPU path behind it.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/vortex_b200.h"
+#include "address_space.h"
+#include "rt_raycast.h"
+#include "rt_rtu.h"
+
+#define VXB_EXPORT extern "C" __attribute__((visibility("default")))
+
+namespace vxb {
+
+static thread_local std::string g_last_error;
+static int g_selected_device = -1;
+
+static int fail(const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  if (getenv("VORTEX_B200_VERBOSE")) fprintf(stderr, "[VXDRV-b200] %s\n", buf);
+  return -1;
+}
+
+#define CUDA_TRY(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) return fail("%s failed: %s", #expr, cudaGetErrorString(_e)); \
+  } while (0)
+
+static uint64_t env_u64(const char *name, uint64_t dflt) {
+  const char *s = getenv(name);
+  if (!s || !*s) return dflt;
+  return strtoull(s, nullptr, 0);
+}
+
+class Device {
+public:
+  Device() : space_(0) {}
+  ~Device() { shutdown(); }
+
+  int init() {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+      return fail("no CUDA device: the b200 backend has no CPU fallback (%s)", e != cudaSuccess ? cudaGetErrorString(e) : "count=0");
+    int dev = g_selected_device;
+    if (dev < 0) dev = (int)env_u64("VORTEX_B200_DEVICE", env_u64("LOCAL_RANK", 0));
+    if (dev >= count) dev = dev % count;
+    cuda_dev_ = dev;
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    CUDA_TRY(cudaGetDeviceProperties(&prop_, cuda_dev_));
+    if (prop_.major < 10 && !getenv("VORTEX_B200_ALLOW_ANY_ARCH"))
+      return fail("device %d is sm_%d%d; this backend is built for sm_100a only", cuda_dev_, prop_.major, prop_.minor);
+    uint64_t cap = env_u64("VORTEX_B200_MEM_GB", 4) << 30;   // GLOBAL_MEM_SIZE of the XLEN=32 build (common.h:36)
+    space_ = AddressSpace(cap);
+    CUDA_TRY(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    CUDA_TRY(cudaMalloc(&arena_, cap));
+    CUDA_TRY(cudaMemsetAsync(arena_, 0, cap, stream_));
+    CUDA_TRY(cudaMalloc(&counters_, sizeof(WorkCounters)));
+    CUDA_TRY(cudaMalloc(&tile_counter_, sizeof(uint32_t)));
+    CUDA_TRY(cudaMallocHost(&h_counters_, sizeof(WorkCounters)));
+    CUDA_TRY(cudaEventCreate(&ev_begin_));
+    CUDA_TRY(cudaEventCreate(&ev_prep_));
+    CUDA_TRY(cudaEventCreate(&ev_end_));
+    part_.rank = (uint32_t)env_u64("VORTEX_B200_RANK", 0);
+    part_.world = (uint32_t)env_u64("VORTEX_B200_WORLD", 1);
+    part_.band_rows = 8;
+    if (part_.world == 0) part_.world = 1;
+    if (part_.rank >= part_.world) return fail("VORTEX_B200_RANK %u >= VORTEX_B200_WORLD %u", part_.rank, part_.world);
+    CUDA_TRY(cudaStreamSynchronize(stream_));
+    return 0;
+  }
+
+  void shutdown() {
+    if (cuda_dev_ < 0) return;
+    cudaSetDevice(cuda_dev_);
+    if (stream_) cudaStreamSynchronize(stream_);
+    if (gtri_) cudaFree(gtri_);
+    if (rtu_) rtu_release(rtu_);
+    if (counters_) cudaFree(counters_);
+    if (tile_counter_) cudaFree(tile_counter_);
+    if (h_counters_) cudaFreeHost(h_counters_);
+    if (arena_) cudaFree(arena_);
+    if (ev_begin_) cudaEventDestroy(ev_begin_);
+    if (ev_prep_) cudaEventDestroy(ev_prep_);
+    if (ev_end_) cudaEventDestroy(ev_end_);
+    if (stream_) cudaStreamDestroy(stream_);
+    gtri_ = nullptr, rtu_ = nullptr, counters_ = nullptr, tile_counter_ = nullptr, h_counters_ = nullptr, arena_ = nullptr;
+    stream_ = nullptr;
+    cuda_dev_ = -1;
+  }
+
+  // ---- capabilities (reference ids: vortex.h:30-44; simx answers: runtime/simx/vortex.cpp:76-133) ----
+  int get_caps(uint32_t id, uint64_t *value) {
+    uint64_t v;
+    switch (id) {
+      case VX_CAPS_VERSION: v = 0xB200; break;
+      case VX_CAPS_NUM_THREADS: v = (uint64_t)prop_.warpSize; break;
+      case VX_CAPS_NUM_WARPS: v = (uint64_t)prop_.maxThreadsPerMultiProcessor / prop_.warpSize; break;
+      case VX_CAPS_NUM_CORES: v = (uint64_t)prop_.multiProcessorCount; break;
+      case VX_CAPS_NUM_CLUSTERS: v = 1; break;
+      case VX_CAPS_SOCKET_SIZE: v = 1; break;
+      case VX_CAPS_ISSUE_WIDTH: v = 4; break;   // 4 SM sub-partitions issue one warp instruction each per clock
+      case VX_CAPS_CACHE_LINE_SIZE: v = 128; break;
+      case VX_CAPS_GLOBAL_MEM_SIZE: v = space_.capacity(); break;
+      case VX_CAPS_LOCAL_MEM_SIZE: v = (uint64_t)prop_.sharedMemPerBlockOptin; break;
+      case VX_CAPS_ISA_FLAGS: v = 0; break;     // not a RISC-V device: no ISA extension bits to advertise
+      case VX_CAPS_NUM_MEM_BANKS: v = (uint64_t)(prop_.memoryBusWidth / 64 > 0 ? prop_.memoryBusWidth / 64 : 1); break;
+      case VX_CAPS_MEM_BANK_SIZE: v = (uint64_t)prop_.totalGlobalMem / (uint64_t)(prop_.memoryBusWidth / 64 > 0 ? prop_.memoryBusWidth / 64 : 1); break;
+      case VX_CAPS_CLOCK_RATE: {
+        int khz = 0;
+        cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, cuda_dev_);
+        v = (uint64_t)khz * 1000ull;
+        break;
+      }
+      case VX_CAPS_PEAK_MEM_BW: {
+        int mem_khz = 0;
+        cudaDeviceGetAttribute(&mem_khz, cudaDevAttrMemoryClockRate, cuda_dev_);
+        v = (uint64_t)(2.0 * mem_khz * 1e3 * (prop_.memoryBusWidth / 8) / 1e6);   // MB/s, DDR
+        break;
+      }
+      default:
+        return fail("invalid caps id %u", id);   // simx aborts here (runtime/simx/vortex.cpp:126-130); we report
+    }
+    *value = v;
+    return 0;
+  }
+
+  // ---- memory ----
+  int mem_alloc(uint64_t size, int flags, uint64_t *addr) {
+    std::lock_guard<std::mutex> g(mu_);
+    if (space_.allocate(size, flags, addr) != 0) return fail("out of device address space (size=%llu)", (unsigned long long)size);
+    return 0;
+  }
+  int mem_reserve(uint64_t addr, uint64_t size, int flags) {
+    std::lock_guard<std::mutex> g(mu_);
+    if (space_.reserve(addr, size, flags) != 0)
+      return fail("cannot reserve [0x%llx, +%llu)", (unsigned long long)addr, (unsigned long long)size);
+    return 0;
+  }
+  int mem_free(uint64_t addr) {
+    std::lock_guard<std::mutex> g(mu_);
+    small_shadow_.erase(addr);
+    if (space_.release(addr) != 0) return fail("release address not found: 0x%llx", (unsigned long long)addr);
+    ++generation_;   // any cached GPU layout keyed on this block is stale now
+    return 0;
+  }
+  int mem_access(uint64_t addr, uint64_t size, int flags) {
+    (void)flags;   // ACL bits are recorded by simx's RAM model; CUDA memory has no per-range ACL
+    uint64_t asize = AddressSpace::align_up(size, AddressSpace::kBlockAlign);
+    if (addr + asize > space_.capacity()) return -1;
+    return 0;
+  }
+  int mem_info(uint64_t *mem_free, uint64_t *mem_used) {
+    std::lock_guard<std::mutex> g(mu_);
+    if (mem_free) *mem_free = space_.free_bytes();
+    if (mem_used) *mem_used = space_.allocated();
+    return 0;
+  }
+
+  int upload(uint64_t dst, const void *src, uint64_t size) {
+    if (size == 0) return 0;
+    std::lock_guard<std::mutex> g(mu_);
+    if (dst + size > space_.capacity() || dst + size < dst) return fail("upload out of range");
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    uint64_t start = 0;
+    if (auto *b = space_.find(dst, size, &start)) {
+      b->write_gen = ++generation_;
+      if (size <= 4096) {
+        auto &sh = small_shadow_[start];
+        if (sh.size() < b->size) sh.resize(b->size, 0);
+        if (dst - start + size <= sh.size()) memcpy(sh.data() + (dst - start), src, size);
+      } else {
+        small_shadow_.erase(start);
+      }
+    }
+    CUDA_TRY(cudaMemcpyAsync(arena_ + dst, src, size, cudaMemcpyHostToDevice, stream_));
+    CUDA_TRY(cudaStreamSynchronize(stream_));
+    return 0;
+  }
+  int download(void *dst, uint64_t src, uint64_t size) {
+    if (size == 0) return 0;
+    std::lock_guard<std::mutex> g(mu_);
+    if (src + size > space_.capacity() || src + size < src) return fail("download out of range");
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    CUDA_TRY(cudaMemcpyAsync(dst, arena_ + src, size, cudaMemcpyDeviceToHost, stream_));
+    CUDA_TRY(cudaStreamSynchronize(stream_));
+    return finish_run_locked();
+  }
+
+  // ---- launch ----
+  int start(uint64_t krnl_addr, uint64_t args_addr) {
+    (void)krnl_addr;   // the RISC-V image is accepted and ignored
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    std::vector<uint8_t> args;
+    if (fetch_args_locked(args_addr, args) != 0) return -1;
+    uint32_t layout = dcr_get(VX_DCR_B200_RT_LAYOUT);
+    if (layout == 0) layout = (args.size() >= sizeof(KernelArgB)) ? 2 : (args.size() >= sizeof(KernelArgA) ? 1 : 0);
+    if (layout == 1) return start_raycast_locked(args, nullptr, nullptr, 0, 0);
+    if (layout == 2) return start_rtu_locked(args);
+    return fail("vx_start: argument block of %zu bytes is neither a raycast (192 B) nor a raytracing (216 B) kernel_arg_t", args.size());
+  }
+
+  int trace(uint64_t args_addr, const uint64_t *rays_addr, uint64_t count, uint64_t hits_addr) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    std::vector<uint8_t> args;
+    if (fetch_args_locked(args_addr, args) != 0) return -1;
+    if (args.size() >= sizeof(KernelArgB) || dcr_get(VX_DCR_B200_RT_LAYOUT) == 2)
+      return trace_rtu_locked(args, rays_addr, count, hits_addr);
+    if (args.size() < sizeof(KernelArgA)) return fail("trace: argument block too small");
+    return start_raycast_locked(args, &hits_addr, rays_addr, count, 1);
+  }
+
+  int ready_wait(uint64_t timeout_ms) {
+    std::lock_guard<std::mutex> g(mu_);
+    if (!run_pending_) return 0;
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    auto t0 = std::chrono::steady_clock::now();
+    for (;;) {
+      cudaError_t q = cudaEventQuery(ev_end_);
+      if (q == cudaSuccess) break;
+      if (q != cudaErrorNotReady) return fail("kernel failed: %s", cudaGetErrorString(q));
+      auto ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+      if ((uint64_t)ms >= timeout_ms) return -1;   // reference: -1 on timeout (runtime/simx/vortex.cpp:350-364)
+      if (ms < 2) std::this_thread::yield();
+      else std::this_thread::sleep_for(std::chrono::microseconds(50));
+    }
+    return finish_run_locked();
+  }
+
+  int dcr_write(uint32_t addr, uint32_t value) {
+    std::lock_guard<std::mutex> g(mu_);
+    // the reference serialises a DCR write behind a running kernel (runtime/simx/vortex.cpp:366-373);
+    // DCRs are sampled at vx_start here, so a write never races a kernel in flight.
+    dcrs_[addr] = value;
+    return 0;
+  }
+  int dcr_read(uint32_t addr, uint32_t *value) {
+    std::lock_guard<std::mutex> g(mu_);
+    auto it = dcrs_.find(addr);
+    if (it == dcrs_.end()) return fail("DCR 0x%x was never written", addr);
+    *value = it->second;
+    return 0;
+  }
+  int mpm_query(uint32_t addr, uint32_t core_id, uint64_t *value) {
+    std::lock_guard<std::mutex> g(mu_);
+    uint32_t off = addr - VX_CSR_MPM_BASE;
+    if (off > 31) return -1;
+    if (core_id >= (uint32_t)prop_.multiProcessorCount) return -1;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, cuda_dev_);
+    if (addr == VX_CSR_MCYCLE) *value = (uint64_t)((double)stats_.kernel_ms * khz);                      // elapsed SM clocks
+    else if (addr == VX_CSR_MINSTRET) *value = stats_.rays / (uint64_t)prop_.multiProcessorCount;        // "retired" = rays per SM
+    else *value = 0;
+    return 0;
+  }
+
+  // ---- extensions ----
+  int set_partition(uint32_t rank, uint32_t world, uint32_t band_rows) {
+    std::lock_guard<std::mutex> g(mu_);
+    if (world == 0 || rank >= world) return fail("bad partition rank=%u world=%u", rank, world);
+    if (band_rows == 0 || band_rows % 4 != 0) return fail("band_rows must be a positive multiple of 4");
+    part_.rank = rank, part_.world = world, part_.band_rows = band_rows;
+    return 0;
+  }
+  uint8_t *arena() const { return arena_; }
+  cudaStream_t stream() const { return stream_; }
+  int cuda_device() const { return cuda_dev_; }
+  void enable_stats(int on) { stats_on_ = on; }
+  int get_stats(vx_b200_stats_t *s) {
+    std::lock_guard<std::mutex> g(mu_);
+    *s = stats_;
+    return 0;
+  }
+  float last_ms() const { return stats_.kernel_ms; }
+
+private:
+  uint32_t dcr_get(uint32_t addr) const {
+    auto it = dcrs_.find(addr);
+    return it == dcrs_.end() ? 0u : it->second;
+  }
+
+  int fetch_args_locked(uint64_t args_addr, std::vector<uint8_t> &out) {
+    uint64_t start = 0;
+    auto *b = space_.find(args_addr, 1, &start);
+    if (!b) return fail("arguments address 0x%llx is not inside a live buffer", (unsigned long long)args_addr);
+    uint64_t avail = b->size - (args_addr - start);
+    if (avail > 4096) avail = 4096;
+    out.resize(avail);
+    auto it = small_shadow_.find(start);
+    if (it != small_shadow_.end() && it->second.size() >= (args_addr - start) + avail) {
+      memcpy(out.data(), it->second.data() + (args_addr - start), avail);   // host copy kept at upload time: no device round trip
+    } else {
+      CUDA_TRY(cudaMemcpyAsync(out.data(), arena_ + args_addr, avail, cudaMemcpyDeviceToHost, stream_));
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+    }
+    return 0;
+  }
+
+  // resolve a Vortex address to a device pointer, requiring `need` bytes inside one live buffer
+  template <class T>
+  int resolve(uint64_t addr, uint64_t need, uint64_t align, const char *what, T **out, uint64_t *avail = nullptr, uint64_t *gen = nullptr) {
+    uint64_t start = 0;
+    auto *b = space_.find(addr, need ? need : 1, &start);
+    if (!b) return fail("%s address 0x%llx (+%llu) is not inside a live buffer", what, (unsigned long long)addr, (unsigned long long)need);
+    if (align && (addr % align) != 0) return fail("%s address 0x%llx is not %llu-byte aligned", what, (unsigned long long)addr, (unsigned long long)align);
+    *out = reinterpret_cast<T *>(arena_ + addr);
+    if (avail) *avail = b->size - (addr - start);
+    if (gen) *gen = b->write_gen;
+    return 0;
+  }
+
+  int begin_run_locked() {
+    if (run_pending_) {   // "ensure prior run completed" (runtime/simx/vortex.cpp:331-333)
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+    }
+    CUDA_TRY(cudaMemsetAsync(counters_, 0, sizeof(WorkCounters), stream_));
+    CUDA_TRY(cudaMemsetAsync(tile_counter_, 0, sizeof(uint32_t), stream_));
+    launches_ = 0, prep_launches_ = 0;
+    CUDA_TRY(cudaEventRecord(ev_begin_, stream_));
+    return 0;
+  }
+  int end_run_locked() {
+    CUDA_TRY(cudaEventRecord(ev_end_, stream_));
+    CUDA_TRY(cudaMemcpyAsync(h_counters_, counters_, sizeof(WorkCounters), cudaMemcpyDeviceToHost, stream_));
+    run_pending_ = true;
+    return 0;
+  }
+  int finish_run_locked() {
+    if (!run_pending_) return 0;
+    CUDA_TRY(cudaStreamSynchronize(stream_));
+    run_pending_ = false;
+    float ms_total = 0, ms_prep = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms_total, ev_begin_, ev_end_));
+    CUDA_TRY(cudaEventElapsedTime(&ms_prep, ev_begin_, ev_prep_));
+    stats_.rays = h_counters_->rays;
+    stats_.box_tests = h_counters_->box_tests;
+    stats_.tri_tests = h_counters_->tri_tests;
+    stats_.blas_entered = h_counters_->blas_entered;
+    stats_.shaded_hits = h_counters_->shaded_hits;
+    stats_.kernel_launches = launches_;
+    stats_.prep_launches = prep_launches_;
+    stats_.prep_ms = ms_prep;
+    stats_.kernel_ms = ms_total - ms_prep;
+    return 0;
+  }
+
+  // layout A: decode kernel_arg_t, (re)build the GPU triangle records if the scene changed, launch
+  int start_raycast_locked(const std::vector<uint8_t> &args, const uint64_t *hits_addr, const uint64_t *rays_addr, uint64_t count, int trace) {
+    KernelArgA a;
+    memcpy(&a, args.data(), sizeof(a));
+    if (a.dst_width == 0 || a.dst_height == 0) return fail("empty framebuffer %ux%u", a.dst_width, a.dst_height);
+    SceneA sc{};
+    const TriA *tri = nullptr;
+    const uint32_t *triIdx = nullptr;
+    uint64_t tri_bytes = 0, idx_bytes = 0, tri_gen = 0, idx_gen = 0;
+    if (resolve(a.tri_addr, sizeof(TriA), 4, "tri", &tri, &tri_bytes, &tri_gen)) return -1;
+    if (resolve(a.triIdx_addr, 4, 4, "triIdx", &triIdx, &idx_bytes, &idx_gen)) return -1;
+    if (resolve(a.triEx_addr, sizeof(TriExA), 4, "triEx", &sc.triEx)) return -1;
+    if (resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &sc.nodes)) return -1;
+    if (resolve(a.blas_addr, sizeof(BlasNodeA), 8, "blas", &sc.blas)) return -1;
+    if (resolve(a.tlas_addr, sizeof(TlasNodeA), 16, "tlas", &sc.tlas)) return -1;
+    if (resolve(a.tex_addr, 4, 4, "tex", &sc.tex)) return -1;
+    sc.tlas_root = a.tlas_root;
+    uint32_t *out = nullptr;
+    HitA *hits = nullptr;
+    const float *rays = nullptr;
+    if (!trace) {
+      if (resolve(a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, 4, "framebuffer", &out)) return -1;
+    } else {
+      uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
+      if (resolve(*hits_addr, n * sizeof(HitA), 4, "hits", &hits)) return -1;
+      if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &rays)) return -1;
+      count = n;
+    }
+    if (begin_run_locked() != 0) return -1;
+    // scene re-flatten, cached on (addresses, last-upload generations)
+    uint64_t n_slots = idx_bytes / 4, n_tris = tri_bytes / sizeof(TriA);
+    if (!gtri_ || gtri_key_[0] != a.tri_addr || gtri_key_[1] != a.triIdx_addr || gtri_key_[2] != tri_gen || gtri_key_[3] != idx_gen ||
+        gtri_slots_ != n_slots) {
+      if (gtri_cap_ < n_slots) {
+        if (gtri_) cudaFree(gtri_);
+        gtri_ = nullptr, gtri_cap_ = 0;
+        CUDA_TRY(cudaMalloc(&gtri_, n_slots * sizeof(GpuTri)));
+        gtri_cap_ = n_slots;
+      }
+      CUDA_TRY(launch_gather_tris(tri, triIdx, gtri_, n_slots, n_tris, stream_));
+      gtri_key_[0] = a.tri_addr, gtri_key_[1] = a.triIdx_addr, gtri_key_[2] = tri_gen, gtri_key_[3] = idx_gen;
+      gtri_slots_ = n_slots;
+      ++launches_, ++prep_launches_;
+    }
+    CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
+    sc.gtri = gtri_;
+    int rc;
+    if (!trace) {
+      RenderA p{};
+      p.scene = sc, p.arg = a, p.out = out, p.part = part_;
+      p.mode = dcr_get(VX_DCR_B200_RT_MODE), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
+      p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
+      rc = launch_render_a(p, prop_.multiProcessorCount, stream_);
+    } else {
+      TraceA p{};
+      p.scene = sc, p.arg = a, p.rays = rays, p.count = count, p.hits = hits;
+      p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER), p.counters = counters_, p.stats = stats_on_;
+      rc = launch_trace_a(p, prop_.multiProcessorCount, stream_);
+    }
+    if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    launches_ += rc;
+    return end_run_locked();
+  }
+
+  int rtu_scene_locked(const KernelArgB &a, RtuScene *sc) {
+    // the RT unit reads its four scene pointers from DCRs 0x006..0x009 (sim/simx/rt_traversal.cpp:35-38);
+    // hosts that never wrote them fall back to the kernel_arg_t fields
+    uint64_t tlas_addr = dcrs_.count(VX_DCR_BASE_RTX_TLAS_PTR) ? dcr_get(VX_DCR_BASE_RTX_TLAS_PTR) : a.tlas_addr;
+    uint64_t blas_addr = dcrs_.count(VX_DCR_BASE_RTX_BLAS_PTR) ? dcr_get(VX_DCR_BASE_RTX_BLAS_PTR) : a.blas_addr;
+    uint64_t qbvh_addr = dcrs_.count(VX_DCR_BASE_RTX_BVH_PTR) ? dcr_get(VX_DCR_BASE_RTX_BVH_PTR) : a.qBvh_addr;
+    uint64_t tri_addr = dcrs_.count(VX_DCR_BASE_RTX_TRI_PTR) ? dcr_get(VX_DCR_BASE_RTX_TRI_PTR) : a.tri_addr;
+    if (resolve(tlas_addr, sizeof(QNodeB), 4, "tlas(q)", &sc->tlas)) return -1;
+    if (resolve(blas_addr, sizeof(BlasNodeB), 4, "blas", &sc->blas)) return -1;
+    if (resolve(qbvh_addr, sizeof(QNodeB), 4, "qBvh", &sc->qbvh)) return -1;
+    if (resolve(tri_addr, sizeof(TriA), 4, "tri", &sc->tri)) return -1;
+    if (resolve(a.triEx_addr, sizeof(TriExB), 4, "triEx", &sc->triEx)) return -1;
+    sc->mat = nullptr, sc->tex = nullptr;
+    if (a.mat_addr) { if (resolve(a.mat_addr, 4, 4, "mat", &sc->mat)) return -1; }
+    if (a.tex_addr) { if (resolve(a.tex_addr, 4, 4, "tex", &sc->tex)) return -1; }
+    sc->tlas_root = a.tlas_root;
+    return 0;
+  }
+
+  int start_rtu_locked(const std::vector<uint8_t> &args) {
+    if (args.size() < sizeof(KernelArgB)) return fail("layout B needs a 216-byte kernel_arg_t");
+    KernelArgB a;
+    memcpy(&a, args.data(), sizeof(a));
+    if (a.dst_width == 0 || a.dst_height == 0) return fail("empty framebuffer");
+    RtuRender p{};
+    if (rtu_scene_locked(a, &p.scene)) return -1;
+    if (resolve(a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, 4, "framebuffer", &p.out)) return -1;
+    if (begin_run_locked() != 0) return -1;
+    CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
+    p.arg = a, p.part = part_, p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
+    p.camera = dcr_get(VX_DCR_B200_RT_CAMERA);
+    int rc = launch_rtu_render(p, prop_.multiProcessorCount, stream_);
+    if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    launches_ += rc;
+    return end_run_locked();
+  }
+
+  int trace_rtu_locked(const std::vector<uint8_t> &args, const uint64_t *rays_addr, uint64_t count, uint64_t hits_addr) {
+    if (args.size() < sizeof(KernelArgB)) return fail("layout B needs a 216-byte kernel_arg_t");
+    KernelArgB a;
+    memcpy(&a, args.data(), sizeof(a));
+    RtuTrace p{};
+    if (rtu_scene_locked(a, &p.scene)) return -1;
+    uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
+    if (resolve(hits_addr, n * sizeof(HitA), 4, "hits", &p.hits)) return -1;
+    p.rays = nullptr;
+    if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &p.rays)) return -1;
+    if (begin_run_locked() != 0) return -1;
+    CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
+    p.arg = a, p.count = n, p.counters = counters_, p.stats = stats_on_;
+    p.camera = dcr_get(VX_DCR_B200_RT_CAMERA);
+    int rc = launch_rtu_trace(p, prop_.multiProcessorCount, stream_);
+    if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    launches_ += rc;
+    return end_run_locked();
+  }
+
+  std::mutex mu_;
+  int cuda_dev_ = -1;
+  cudaDeviceProp prop_{};
+  cudaStream_t stream_ = nullptr;
+  uint8_t *arena_ = nullptr;
+  AddressSpace space_;
+  uint64_t generation_ = 0;
+  std::unordered_map<uint64_t, std::vector<uint8_t>> small_shadow_;   // host copies of small uploads (argument blocks)
+  std::unordered_map<uint32_t, uint32_t> dcrs_;
+  Partition part_;
+  // layout-A GPU triangle records
+  GpuTri *gtri_ = nullptr;
+  uint64_t gtri_cap_ = 0, gtri_slots_ = 0;
+  uint64_t gtri_key_[4] = {0, 0, 0, 0};
+  void *rtu_ = nullptr;
+  // run bookkeeping
+  WorkCounters *counters_ = nullptr, *h_counters_ = nullptr;
+  uint32_t *tile_counter_ = nullptr;
+  cudaEvent_t ev_begin_ = nullptr, ev_prep_ = nullptr, ev_end_ = nullptr;
+  bool run_pending_ = false;
+  uint64_t launches_ = 0, prep_launches_ = 0;
+  int stats_on_ = 0;
+  vx_b200_stats_t stats_{};
+};
+
+struct Buffer {   // what a vx_buffer_h points at (reference: callbacks.inc:14-18)
+  Device *device;
+  uint64_t addr;
+  uint64_t size;
+};
+
+}  // namespace vxb
+
+using vxb::Buffer;
+using vxb::Device;
+using vxb::fail;
+
+// =====================================================================================================
+// C ABI (2): the runtime calls.  Argument checks follow runtime/common/callbacks.inc line by line.
+// =====================================================================================================
+static int b200_open(vx_device_h *hdevice) {
+  if (!hdevice) return -1;
+  auto d = new Device();
+  if (d->init() != 0) {
+    std::string keep = vxb::g_last_error;
+    delete d;
+    vxb::g_last_error = keep;
+    return -1;
+  }
+  *hdevice = d;
+  return 0;
+}
+
+VXB_EXPORT int vx_dev_close(vx_device_h hdevice) {
+  if (!hdevice) return -1;
+  if (getenv("VORTEX_B200_PERF")) vx_dump_perf(hdevice, stdout);
+  delete (Device *)hdevice;
+  return 0;
+}
+
+VXB_EXPORT int vx_dev_caps(vx_device_h hdevice, uint32_t caps_id, uint64_t *value) {
+  if (!hdevice || !value) return -1;
+  return ((Device *)hdevice)->get_caps(caps_id, value);
+}
+
+VXB_EXPORT int vx_mem_alloc(vx_device_h hdevice, uint64_t size, int flags, vx_buffer_h *hbuffer) {
+  if (!hdevice || !hbuffer || size == 0) return -1;
+  auto d = (Device *)hdevice;
+  uint64_t addr;
+  if (d->mem_alloc(size, flags, &addr) != 0) return -1;
+  *hbuffer = new Buffer{d, addr, size};
+  return 0;
+}
+
+VXB_EXPORT int vx_mem_reserve(vx_device_h hdevice, uint64_t address, uint64_t size, int flags, vx_buffer_h *hbuffer) {
+  if (!hdevice || !hbuffer || size == 0) return -1;
+  auto d = (Device *)hdevice;
+  if (d->mem_reserve(address, size, flags) != 0) return -1;
+  *hbuffer = new Buffer{d, address, size};
+  return 0;
+}
+
+VXB_EXPORT int vx_mem_free(vx_buffer_h hbuffer) {
+  if (!hbuffer) return 0;   // reference: freeing a null handle succeeds (callbacks.inc:100-101)
+  auto b = (Buffer *)hbuffer;
+  int err = b->device->mem_free(b->addr);
+  delete b;
+  return err;
+}
+
+VXB_EXPORT int vx_mem_access(vx_buffer_h hbuffer, uint64_t offset, uint64_t size, int flags) {
+  if (!hbuffer) return -1;
+  auto b = (Buffer *)hbuffer;
+  if (offset + size > b->size) return -1;
+  return b->device->mem_access(b->addr + offset, size, flags);
+}
+
+VXB_EXPORT int vx_mem_address(vx_buffer_h hbuffer, uint64_t *address) {
+  if (!hbuffer || !address) return -1;
+  *address = ((Buffer *)hbuffer)->addr;
+  return 0;
+}
+
+VXB_EXPORT int vx_mem_info(vx_device_h hdevice, uint64_t *mem_free, uint64_t *mem_used) {
+  if (!hdevice) return -1;
+  return ((Device *)hdevice)->mem_info(mem_free, mem_used);
+}
+
+VXB_EXPORT int vx_copy_to_dev(vx_buffer_h hbuffer, const void *host_ptr, uint64_t dst_offset, uint64_t size) {
+  if (!hbuffer || !host_ptr) return -1;
+  auto b = (Buffer *)hbuffer;
+  if (dst_offset + size > b->size) return -1;
+  return b->device->upload(b->addr + dst_offset, host_ptr, size);
+}
+
+VXB_EXPORT int vx_copy_from_dev(void *host_ptr, vx_buffer_h hbuffer, uint64_t src_offset, uint64_t size) {
+  if (!hbuffer || !host_ptr) return -1;
+  auto b = (Buffer *)hbuffer;
+  if (src_offset + size > b->size) return -1;
+  return b->device->download(host_ptr, b->addr + src_offset, size);
+}
+
+VXB_EXPORT int vx_start(vx_device_h hdevice, vx_buffer_h hkernel, vx_buffer_h harguments) {
+  if (!hdevice || !hkernel || !harguments) return -1;
+  return ((Device *)hdevice)->start(((Buffer *)hkernel)->addr, ((Buffer *)harguments)->addr);
+}
+
+VXB_EXPORT int vx_ready_wait(vx_device_h hdevice, uint64_t timeout) {
+  if (!hdevice) return -1;
+  return ((Device *)hdevice)->ready_wait(timeout);
+}
+
+VXB_EXPORT int vx_dcr_read(vx_device_h hdevice, uint32_t addr, uint32_t *value) {
+  if (!hdevice || !value) return -1;
+  return ((Device *)hdevice)->dcr_read(addr, value);
+}
+
+VXB_EXPORT int vx_dcr_write(vx_device_h hdevice, uint32_t addr, uint32_t value) {
+  if (!hdevice) return -1;
+  return ((Device *)hdevice)->dcr_write(addr, value);
+}
+
+VXB_EXPORT int vx_mpm_query(vx_device_h hdevice, uint32_t addr, uint32_t core_id, uint64_t *value) {
+  if (!hdevice || !value) return -1;
+  return ((Device *)hdevice)->mpm_query(addr, core_id, value);
+}
+
+VXB_EXPORT int vx_dev_open(vx_device_h *hdevice) {
+  // the stub opens the driver and then programs five DCRs (runtime/stub/vortex.cpp:25-49,84-91)
+  vx_device_h h;
+  if (b200_open(&h) != 0) return -1;
+  vx_dcr_write(h, VX_DCR_BASE_STARTUP_ADDR0, 0x80000000u);
+  vx_dcr_write(h, VX_DCR_BASE_STARTUP_ADDR1, 0);
+  vx_dcr_write(h, VX_DCR_BASE_STARTUP_ARG0, 0);
+  vx_dcr_write(h, VX_DCR_BASE_STARTUP_ARG1, 0);
+  vx_dcr_write(h, VX_DCR_BASE_MPM_CLASS, 0);
+  *hdevice = h;
+  return 0;
+}
+
+// ---- upload helpers (reference: runtime/stub/utils.cpp:25-122) ----
+VXB_EXPORT int vx_upload_kernel_bytes(vx_device_h hdevice, const void *content, uint64_t size, vx_buffer_h *hbuffer) {
+  if (!hdevice || !content || size <= 8 || !hbuffer) return -1;
+  if (size < 16) return -1;
+  uint64_t vma[2];
+  memcpy(vma, content, 16);   // image header: {min_vma, max_vma}
+  uint64_t bin_size = size - 16, runtime_size = vma[1] - vma[0];
+  if (vma[1] <= vma[0] || bin_size > runtime_size) return fail("malformed kernel image header");
+  vx_buffer_h buf;
+  if (vx_mem_reserve(hdevice, vma[0], runtime_size, 0, &buf) != 0) return -1;
+  if (vx_mem_access(buf, 0, bin_size, VX_MEM_READ) != 0 || vx_mem_access(buf, bin_size, runtime_size - bin_size, VX_MEM_READ_WRITE) != 0 ||
+      (bin_size && vx_copy_to_dev(buf, (const uint8_t *)content + 16, 0, bin_size) != 0)) {
+    vx_mem_free(buf);
+    return -1;
+  }
+  *hbuffer = buf;
+  return 0;
+}
+
+static int read_file(const char *filename, std::vector<char> &content) {
+  std::ifstream ifs(filename, std::ios::binary);
+  if (!ifs) {
+    fprintf(stderr, "Error: %s not found\n", filename);
+    return -1;
+  }
+  ifs.seekg(0, ifs.end);
+  auto size = ifs.tellg();
+  content.resize((size_t)size);
+  ifs.seekg(0, ifs.beg);
+  ifs.read(content.data(), size);
+  return 0;
+}
+
+VXB_EXPORT int vx_upload_kernel_file(vx_device_h hdevice, const char *filename, vx_buffer_h *hbuffer) {
+  if (!hdevice || !filename || !hbuffer) return -1;
+  std::vector<char> content;
+  if (read_file(filename, content) != 0) return -1;
+  return vx_upload_kernel_bytes(hdevice, content.data(), content.size(), hbuffer);
+}
+
+VXB_EXPORT int vx_upload_bytes(vx_device_h hdevice, const void *content, uint64_t size, vx_buffer_h *hbuffer) {
+  if (!hdevice || !content || size == 0 || !hbuffer) return -1;
+  vx_buffer_h buf;
+  if (vx_mem_alloc(hdevice, size, VX_MEM_READ, &buf) != 0) return -1;
+  if (vx_copy_to_dev(buf, content, 0, size) != 0) {
+    vx_mem_free(buf);
+    return -1;
+  }
+  *hbuffer = buf;
+  return 0;
+}
+
+VXB_EXPORT int vx_upload_file(vx_device_h hdevice, const char *filename, vx_buffer_h *hbuffer) {
+  if (!hdevice || !filename || !hbuffer) return -1;
+  std::vector<char> content;
+  if (read_file(filename, content) != 0) return -1;
+  return vx_upload_bytes(hdevice, content.data(), content.size(), hbuffer);
+}
+
+VXB_EXPORT int vx_dump_perf(vx_device_h hdevice, FILE *stream) {
+  if (!hdevice || !stream) return -1;
+  vx_b200_stats_t s;
+  ((Device *)hdevice)->get_stats(&s);
+  double mrays = s.kernel_ms > 0 ? (double)s.rays / (s.kernel_ms * 1e3) : 0.0;
+  fprintf(stream, "PERF: rays=%llu, kernel_ms=%.4f, Mrays/s=%.1f, launches=%llu, prep_ms=%.4f\n", (unsigned long long)s.rays, s.kernel_ms,
+          mrays, (unsigned long long)s.kernel_launches, s.prep_ms);
+  if (s.box_tests || s.tri_tests)
+    fprintf(stream, "PERF: box_tests=%llu, tri_tests=%llu, blas_entered=%llu, shaded_hits=%llu\n", (unsigned long long)s.box_tests,
+            (unsigned long long)s.tri_tests, (unsigned long long)s.blas_entered, (unsigned long long)s.shaded_hits);
+  return 0;
+}
+
+// =====================================================================================================
+// C ABI (1): the dispatcher hook
+// =====================================================================================================
+VXB_EXPORT int vx_dev_init(callbacks_t *cb) {
+  if (!cb) return -1;
+  cb->dev_open = b200_open;   // the stub programs the start-up DCRs itself after this returns
+  cb->dev_close = [](vx_device_h h) -> int {
+    if (!h) return -1;
+    delete (Device *)h;
+    return 0;
+  };
+  cb->dev_caps = vx_dev_caps;
+  cb->mem_alloc = vx_mem_alloc;
+  cb->mem_reserve = vx_mem_reserve;
+  cb->mem_free = vx_mem_free;
+  cb->mem_access = vx_mem_access;
+  cb->mem_address = vx_mem_address;
+  cb->mem_info = vx_mem_info;
+  cb->copy_to_dev = vx_copy_to_dev;
+  cb->copy_from_dev = vx_copy_from_dev;
+  cb->start = vx_start;
+  cb->ready_wait = vx_ready_wait;
+  cb->dcr_read = vx_dcr_read;
+  cb->dcr_write = vx_dcr_write;
+  cb->mpm_query = vx_mpm_query;
+  return 0;
+}
+
+// =====================================================================================================
+// C ABI (3): extensions
+// =====================================================================================================
+VXB_EXPORT int vx_b200_select_device(int cuda_device) {
+  vxb::g_selected_device = cuda_device;
+  return 0;
+}
+VXB_EXPORT int vx_b200_set_partition(vx_device_h h, uint32_t rank, uint32_t world, uint32_t band_rows) {
+  if (!h) return -1;
+  return ((Device *)h)->set_partition(rank, world, band_rows);
+}
+VXB_EXPORT int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr) {
+  if (!hbuffer || !cuda_ptr) return -1;
+  auto b = (Buffer *)hbuffer;
+  *cuda_ptr = (uint64_t)(uintptr_t)(b->device->arena() + b->addr);
+  return 0;
+}
+VXB_EXPORT int vx_b200_stream(vx_device_h h, uint64_t *cuda_stream) {
+  if (!h || !cuda_stream) return -1;
+  *cuda_stream = (uint64_t)(uintptr_t)((Device *)h)->stream();
+  return 0;
+}
+VXB_EXPORT int vx_b200_last_kernel_ms(vx_device_h h, float *ms) {
+  if (!h || !ms) return -1;
+  *ms = ((Device *)h)->last_ms();
+  return 0;
+}
+VXB_EXPORT int vx_b200_enable_stats(vx_device_h h, int enable) {
+  if (!h) return -1;
+  ((Device *)h)->enable_stats(enable);
+  return 0;
+}
+VXB_EXPORT int vx_b200_get_stats(vx_device_h h, vx_b200_stats_t *stats) {
+  if (!h || !stats) return -1;
+  return ((Device *)h)->get_stats(stats);
+}
+VXB_EXPORT int vx_b200_trace_primary(vx_device_h h, vx_buffer_h harguments, vx_buffer_h hhits) {
+  if (!h || !harguments || !hhits) return -1;
+  return ((Device *)h)->trace(((Buffer *)harguments)->addr, nullptr, 0, ((Buffer *)hhits)->addr);
+}
+VXB_EXPORT int vx_b200_trace_rays(vx_device_h h, vx_buffer_h harguments, vx_buffer_h hrays, uint64_t count, vx_buffer_h hhits) {
+  if (!h || !harguments || !hrays || !hhits) return -1;
+  if (count == 0) return 0;
+  uint64_t ra = ((Buffer *)hrays)->addr;
+  return ((Device *)h)->trace(((Buffer *)harguments)->addr, &ra, count, ((Buffer *)hhits)->addr);
+}
+VXB_EXPORT const char *vx_b200_last_error(void) { return vxb::g_last_error.c_str(); }

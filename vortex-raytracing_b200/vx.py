@@ -1,0 +1,230 @@
+"""ctypes binding of libvortex-b200.so — the vx_* runtime C ABI (include/vortex_b200.h).
+
+Function names, argument order and error behaviour are the reference's (runtime/include/vortex.h:80-145):
+every call returns 0 on success; this wrapper raises VxError on a non-zero return.  There is no CPU
+fallback: loading fails loudly when the CUDA library has not been built, and vx_dev_open() fails when no
+B200 is visible.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvortex-b200.so")
+
+VX_MEM_READ, VX_MEM_WRITE, VX_MEM_READ_WRITE = 1, 2, 3
+VX_MAX_TIMEOUT = 24 * 60 * 60 * 1000
+VX_DCR_BASE_RTX_TLAS_PTR, VX_DCR_BASE_RTX_BLAS_PTR, VX_DCR_BASE_RTX_BVH_PTR, VX_DCR_BASE_RTX_TRI_PTR = 6, 7, 8, 9
+VX_DCR_B200_RT_MODE, VX_DCR_B200_RT_LAYOUT, VX_DCR_B200_RT_ORDER, VX_DCR_B200_RT_CAMERA = 0x0F0, 0x0F1, 0x0F2, 0x0F3
+MODE_SHADOW, MODE_DIFFUSE = 1, 2
+
+# every symbol include/vortex_b200.h declares (tests check that the library exports all of them)
+EXPORTS = (
+    "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
+    "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
+    "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
+    "vx_b200_select_device vx_b200_set_partition vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_last_error"
+).split()
+
+
+class VxError(RuntimeError):
+    pass
+
+
+class Stats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64), ("blas_entered", C.c_uint64),
+                ("shaded_hits", C.c_uint64), ("kernel_launches", C.c_uint64), ("prep_launches", C.c_uint64),
+                ("kernel_ms", C.c_float), ("prep_ms", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA backend.  Raises if it was not built (run __graft_entry__.build() or make -C csrc)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise VxError(f"{LIB_PATH} is missing: build it with `make -C vortex-raytracing_b200/csrc` "
+                          "(the b200 backend has no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        H, B, u64, u32, i32, vp = C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_void_p
+        sig = {
+            "vx_dev_open": [C.POINTER(H)], "vx_dev_close": [H], "vx_dev_caps": [H, u32, C.POINTER(u64)],
+            "vx_mem_alloc": [H, u64, i32, C.POINTER(B)], "vx_mem_reserve": [H, u64, u64, i32, C.POINTER(B)],
+            "vx_mem_free": [B], "vx_mem_access": [B, u64, u64, i32], "vx_mem_address": [B, C.POINTER(u64)],
+            "vx_mem_info": [H, C.POINTER(u64), C.POINTER(u64)], "vx_copy_to_dev": [B, vp, u64, u64],
+            "vx_copy_from_dev": [vp, B, u64, u64], "vx_start": [H, B, B], "vx_ready_wait": [H, u64],
+            "vx_dcr_read": [H, u32, C.POINTER(u32)], "vx_dcr_write": [H, u32, u32], "vx_mpm_query": [H, u32, u32, C.POINTER(u64)],
+            "vx_upload_kernel_bytes": [H, vp, u64, C.POINTER(B)], "vx_upload_kernel_file": [H, C.c_char_p, C.POINTER(B)],
+            "vx_upload_bytes": [H, vp, u64, C.POINTER(B)], "vx_upload_file": [H, C.c_char_p, C.POINTER(B)],
+            "vx_b200_select_device": [i32], "vx_b200_set_partition": [H, u32, u32, u32], "vx_b200_device_ptr": [B, C.POINTER(u64)],
+            "vx_b200_stream": [H, C.POINTER(u64)], "vx_b200_last_kernel_ms": [H, C.POINTER(C.c_float)],
+            "vx_b200_enable_stats": [H, i32], "vx_b200_get_stats": [H, C.POINTER(Stats)],
+            "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
+        }
+        for name, args in sig.items():
+            f = getattr(L, name)
+            f.argtypes = args
+            f.restype = C.c_int
+        L.vx_b200_last_error.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = lib().vx_b200_last_error().decode(errors="replace")
+        raise VxError(f"{what} returned {rc}" + (f": {msg}" if msg else ""))
+
+
+def _ptr(a):
+    if isinstance(a, np.ndarray):
+        if not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("host array must be C-contiguous")
+        return a.ctypes.data, a.nbytes, a
+    if isinstance(a, (bytes, bytearray)):
+        buf = (C.c_char * len(a)).from_buffer_copy(a)
+        return C.addressof(buf), len(a), buf
+    if isinstance(a, tuple):   # (address, nbytes): e.g. a pinned torch tensor's data_ptr()
+        return a[0], a[1], None
+    raise TypeError(type(a))
+
+
+class Buffer:
+    def __init__(self, dev, handle, size):
+        self.dev, self.h, self.size = dev, handle, size
+
+    @property
+    def address(self):
+        v = C.c_uint64()
+        _check(lib().vx_mem_address(self.h, C.byref(v)), "vx_mem_address")
+        return v.value
+
+    @property
+    def device_ptr(self):
+        v = C.c_uint64()
+        _check(lib().vx_b200_device_ptr(self.h, C.byref(v)), "vx_b200_device_ptr")
+        return v.value
+
+    def copy_to_dev(self, host, dst_offset=0):
+        p, n, _keep = _ptr(host)
+        _check(lib().vx_copy_to_dev(self.h, p, dst_offset, n), "vx_copy_to_dev")
+
+    def copy_from_dev(self, host, src_offset=0):
+        p, n, _keep = _ptr(host)
+        _check(lib().vx_copy_from_dev(p, self.h, src_offset, n), "vx_copy_from_dev")
+
+    def free(self):
+        if self.h:
+            _check(lib().vx_mem_free(self.h), "vx_mem_free")
+            self.h = None
+
+
+class Device:
+    """vx_device_h with the reference's call names as methods."""
+
+    def __init__(self, cuda_device=None):
+        L = lib()
+        if cuda_device is not None:
+            L.vx_b200_select_device(int(cuda_device))
+        h = C.c_void_p()
+        _check(L.vx_dev_open(C.byref(h)), "vx_dev_open")
+        self.h = h
+
+    def close(self):
+        if self.h:
+            _check(lib().vx_dev_close(self.h), "vx_dev_close")
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def caps(self, caps_id):
+        v = C.c_uint64()
+        _check(lib().vx_dev_caps(self.h, caps_id, C.byref(v)), "vx_dev_caps")
+        return v.value
+
+    def mem_alloc(self, size, flags=VX_MEM_READ_WRITE):
+        b = C.c_void_p()
+        _check(lib().vx_mem_alloc(self.h, size, flags, C.byref(b)), "vx_mem_alloc")
+        return Buffer(self, b, size)
+
+    def mem_reserve(self, address, size, flags=0):
+        b = C.c_void_p()
+        _check(lib().vx_mem_reserve(self.h, address, size, flags, C.byref(b)), "vx_mem_reserve")
+        return Buffer(self, b, size)
+
+    def mem_info(self):
+        f, u = C.c_uint64(), C.c_uint64()
+        _check(lib().vx_mem_info(self.h, C.byref(f), C.byref(u)), "vx_mem_info")
+        return f.value, u.value
+
+    def upload_bytes(self, host):
+        p, n, _keep = _ptr(host)
+        b = C.c_void_p()
+        _check(lib().vx_upload_bytes(self.h, p, n, C.byref(b)), "vx_upload_bytes")
+        return Buffer(self, b, n)
+
+    def upload_kernel_bytes(self, content):
+        p, n, _keep = _ptr(content)
+        b = C.c_void_p()
+        _check(lib().vx_upload_kernel_bytes(self.h, p, n, C.byref(b)), "vx_upload_kernel_bytes")
+        return Buffer(self, b, n)
+
+    def start(self, kernel, arguments):
+        _check(lib().vx_start(self.h, kernel.h, arguments.h), "vx_start")
+
+    def ready_wait(self, timeout=VX_MAX_TIMEOUT):
+        _check(lib().vx_ready_wait(self.h, timeout), "vx_ready_wait")
+
+    def dcr_write(self, addr, value):
+        _check(lib().vx_dcr_write(self.h, addr, value), "vx_dcr_write")
+
+    def dcr_read(self, addr):
+        v = C.c_uint32()
+        _check(lib().vx_dcr_read(self.h, addr, C.byref(v)), "vx_dcr_read")
+        return v.value
+
+    def mpm_query(self, addr, core_id=0):
+        v = C.c_uint64()
+        _check(lib().vx_mpm_query(self.h, addr, core_id, C.byref(v)), "vx_mpm_query")
+        return v.value
+
+    # ---- b200 extensions ----
+    def set_partition(self, rank, world, band_rows=8):
+        _check(lib().vx_b200_set_partition(self.h, rank, world, band_rows), "vx_b200_set_partition")
+
+    def stream(self):
+        v = C.c_uint64()
+        _check(lib().vx_b200_stream(self.h, C.byref(v)), "vx_b200_stream")
+        return v.value
+
+    def last_kernel_ms(self):
+        v = C.c_float()
+        _check(lib().vx_b200_last_kernel_ms(self.h, C.byref(v)), "vx_b200_last_kernel_ms")
+        return v.value
+
+    def enable_stats(self, on=True):
+        _check(lib().vx_b200_enable_stats(self.h, int(on)), "vx_b200_enable_stats")
+
+    def stats(self):
+        s = Stats()
+        _check(lib().vx_b200_get_stats(self.h, C.byref(s)), "vx_b200_get_stats")
+        return {n: getattr(s, n) for n, _ in Stats._fields_}
+
+    def trace_primary(self, arguments, hits):
+        _check(lib().vx_b200_trace_primary(self.h, arguments.h, hits.h), "vx_b200_trace_primary")
+
+    def trace_rays(self, arguments, rays, count, hits):
+        _check(lib().vx_b200_trace_rays(self.h, arguments.h, rays.h, count, hits.h), "vx_b200_trace_rays")
+
+
+# a minimal stand-in for kernel.vxbin: {min_vma, max_vma} header + 1 byte (runtime/stub/utils.cpp:25-61).
+# The b200 backend reserves the range like any driver and never executes the image.
+DUMMY_KERNEL_IMAGE = np.array([0x80000000, 0x80001000], dtype=np.uint64).tobytes() + b"\x00" * 16
