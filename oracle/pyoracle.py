@@ -179,6 +179,20 @@ class Scene:
         nrays = self.o._g("render")(karg.ctypes.data, out.ctypes.data, mode, y0, y1, threads)
         return out, int(nrays)
 
+    def render_counted(self, karg=None, mode=0, threads=1):
+        """render + work counters {rays, box_tests, tri_tests, blas_entered, shaded_hits} (oracle port only)."""
+        if self.o.p != "port":
+            raise RuntimeError("work counters exist only in the C port (the reference sources are compiled unmodified)")
+        karg = self.karg if karg is None else karg
+        w, h = int(karg["dst_width"][0]), int(karg["dst_height"][0])
+        out = np.zeros((h, w), dtype=np.uint32)
+        cnt = np.zeros(5, dtype=np.uint64)
+        f = self.o.lib.port_render_counted
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
+        f.restype = None
+        f(karg.ctypes.data, out.ctypes.data, mode, 0, h, threads, cnt.ctypes.data)
+        return out, dict(zip(("rays", "box_tests", "tri_tests", "blas_entered", "shaded_hits"), (int(x) for x in cnt)))
+
     def trace_primary(self, karg=None, want_rays=False, threads=1):
         karg = self.karg if karg is None else karg
         w, h = int(karg["dst_width"][0]), int(karg["dst_height"][0])
@@ -195,6 +209,30 @@ class Scene:
         return hits
 
 
+class RawScene:
+    """The hot path of an oracle run on caller-held buffers (the bytes a host uploaded), not on a scene it built:
+    kernel_arg_t address fields are pointed at the numpy arrays, as the reference's use_cpu_ path does
+    (raycast/tracer.cpp:102-109)."""
+
+    _ADDR = {"tri": "tri_addr", "triEx": "triEx_addr", "triIdx": "triIdx_addr", "tlas": "tlas_addr", "blas": "blas_addr",
+             "bvh": "bvh_addr", "tex": "tex_addr"}
+
+    def __init__(self, oracle, buffers, karg):
+        self.o = oracle
+        self.bufs = {n: np.ascontiguousarray(buffers[n]).view(np.uint8).copy() for n in BUFFER_NAMES}
+        self.karg = np.array(karg, dtype=KARG_DT).reshape(1).copy()
+        for n, f in self._ADDR.items():
+            self.karg[f] = self.bufs[n].ctypes.data
+        self.karg["dst_addr"] = 0
+
+    render = Scene.render
+    trace_primary = Scene.trace_primary
+    trace_rays = Scene.trace_rays
+
+    def render_counted(self, mode=0, threads=1):
+        return Scene.render_counted(self, mode=mode, threads=threads)
+
+
 def RefRaycast():
     return _Raycast(REF_SO, "ref")
 
@@ -205,3 +243,12 @@ def PortRaycast():
 
 def have_ref():
     return os.path.exists(REF_SO)
+
+
+def have_port():
+    return os.path.exists(PORT_SO)
+
+
+def best():
+    """The strongest checker available: the compiled reference when present, else the C port."""
+    return RefRaycast() if have_ref() else PortRaycast()

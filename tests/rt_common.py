@@ -19,6 +19,10 @@ def pyoracle():
     return importlib.import_module("oracle.pyoracle")
 
 
+def best_oracle():
+    return pyoracle().best()
+
+
 def channel_diff(a, b):
     """max per-channel |a-b| of two 0x00RRGGBB images"""
     d = 0
@@ -43,3 +47,22 @@ def hit_parity(gpu, ref):
     return {"n": n, "mismatch": len(bad), "mismatch_frac": len(bad) / max(n, 1), "ties": int(tie.sum()),
             "non_tie": int(len(bad) - tie.sum()), "max_rel_t": float(rel[same & both].max()) if (same & both).any() else 0.0,
             "bit_exact_t": int((gpu["dist"][same] == ref["dist"][same]).sum()), "same": int(same.sum())}
+
+
+def tracer_for(sc, karg, cuda_device=None):
+    """A vx_* Tracer holding exactly the bytes of oracle scene `sc` (after sc.setup -> karg)."""
+    w, h = int(karg["dst_width"][0]), int(karg["dst_height"][0])
+    tr = tracer_mod.Tracer(w, h, int(karg["samples_per_pixel"][0]), int(karg["max_depth"][0]), cuda_device=cuda_device)
+    bufs = sc.buffers() if hasattr(sc, "buffers") else sc.bufs
+    tr.init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names})
+    return tr
+
+
+def assert_hit_gates(hp, strict):
+    """north_star gates: IDs bit-exact on >= 99.99 % of rays, residue = equal-t ties; t within 1e-5 relative."""
+    assert hp["non_tie"] == 0, hp
+    assert hp["mismatch_frac"] <= 1e-4, hp
+    assert hp["max_rel_t"] <= 1e-5, hp
+    if strict:
+        assert hp["mismatch"] == 0 and hp["bit_exact_t"] == hp["n"], hp

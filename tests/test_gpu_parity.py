@@ -1,0 +1,209 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the vx_* C ABI of libvortex-b200.so, against the CPU
+oracle (the compiled reference oracle/_ref when it travelled with the snapshot, else the C port) and the golden fixtures.
+
+Gates (BASELINE.json north_star): closest-hit IDs bit-exact on >= 99.99 % of rays with the residue attributed to equal-t
+ties; t within 1e-5 relative; pixel colour within 1/255 per channel.  In strict order (VX_DCR_B200_RT_ORDER=1, the
+reference's own visiting order) everything is required to be bit-identical."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from rt_common import ROOT, assert_hit_gates, best_oracle, channel_diff, hit_parity, pyoracle, scenes, tracer_for, tracer_mod, vx
+
+pytestmark = pytest.mark.gpu
+po = pyoracle()
+GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")))
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    return best_oracle()
+
+
+def check_render(tr, sc, mode, strict, tol):
+    tr.set_mode(mode, strict)
+    img = tr.run()
+    ref, _ = sc.render(mode=mode, threads=sc.o.hw_threads())
+    d = channel_diff(img, ref)
+    assert d <= tol, f"max channel diff {d} (mode={mode} strict={strict})"
+    return img, ref
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+@pytest.mark.parametrize("strict", [1, 0])
+def test_golden_fixtures(oracle, path, strict):
+    """the reference's own outputs on the reference's own upload bytes"""
+    z = np.load(path)
+    g = {k: z[k] for k in z.files}
+    karg = g["karg"].view(po.KARG_DT).copy()
+    hits_ref = g["hits"].view(po.HIT_DT)
+    rs = po.RawScene(oracle, g, karg)
+    tr = tracer_for(rs, karg)
+    try:
+        tr.set_mode(int(g["mode"]), strict)
+        img = tr.run()
+        d = channel_diff(img, g["image"])
+        assert d <= (0 if strict else 1), d
+        hp = hit_parity(tr.trace_primary(), hits_ref)
+        assert_hit_gates(hp, strict)
+        if strict:
+            assert np.array_equal(img, g["image"])
+    finally:
+        tr.close()
+
+
+CASES = [
+    # name, meshes, w, h, depth, mode, setup kwargs
+    ("cornell64_cfg0", lambda: [scenes.cornell_box()], 64, 64, 1, 0, {}),
+    ("cornell_mirror", lambda: [scenes.cornell_box(0.5)], 160, 120, 4, 0, {}),
+    ("hf224_shadow_cfg1", lambda: [scenes.heightfield(224)], 480, 270, 1, 1, {}),
+    ("hf64_diffuse4_cfg2", lambda: [scenes.heightfield(64)], 192, 108, 4, 2, {}),
+    ("multi_mirror", lambda: [scenes.heightfield(16), scenes.icosphere((0, 0.5, 0), 0.4, 2, reflectivity=0.5), scenes.cornell_box(0.3)],
+     320, 240, 3, 0, {}),
+    ("multi_shadow_diffuse", lambda: [scenes.heightfield(16), scenes.icosphere((0, 0.5, 0), 0.4, 2), scenes.cornell_box()],
+     160, 120, 3, 3, {}),
+    ("ragged_37x19", lambda: [scenes.heightfield(8)], 37, 19, 1, 0, {}),       # width/height not multiples of the 8x4 tile
+    ("one_pixel", lambda: [scenes.cornell_box()], 1, 1, 1, 0, {}),
+    ("spp3", lambda: [scenes.cornell_box(0.2)], 40, 24, 2, 0, {"spp": 3}),      # spp > 1 sums samples (no division), as the reference
+]
+
+
+@pytest.mark.parametrize("name,mk,w,h,depth,mode,kw", CASES, ids=[c[0] for c in CASES])
+def test_render_and_hits_vs_oracle(oracle, name, mk, w, h, depth, mode, kw):
+    sc = oracle.scene_create(mk())
+    karg = sc.setup(w, h, max_depth=depth, **kw)
+    tr = tracer_for(sc, karg)
+    try:
+        img_s, ref = check_render(tr, sc, mode, 1, 0)
+        assert np.array_equal(img_s, ref)
+        check_render(tr, sc, mode, 0, 1)
+        ref_hits = sc.trace_primary(threads=oracle.hw_threads())
+        for strict in (1, 0):
+            tr.set_mode(mode, strict)
+            assert_hit_gates(hit_parity(tr.trace_primary(), ref_hits), strict)
+        st = tr.dev.stats()
+        assert st["rays"] == w * h and st["kernel_launches"] >= 1
+    finally:
+        tr.close()
+
+
+def test_incoherent_and_edge_rays(oracle):
+    """caller-supplied rays: uniform random directions (config 5 shape, small) + axis-parallel / on-plane / grazing rays"""
+    sc = oracle.scene_create([scenes.heightfield(96), scenes.cornell_box()])
+    karg = sc.setup(16, 16, rotate_scene=False)
+    rays = scenes.random_rays(200_000, (-1.5, -1.2, -1.5), (1.5, 1.2, 1.5), seed=5)
+    o = np.array([[0, 0, -3], [-1, 0, -3], [1, 1, -3], [0, -1, -3], [0.25, 0.999, -3], [0, 0, 0], [-1, -1, -1], [0, 5, 0]], dtype=np.float32)
+    d = np.array([[0, 0, 1], [0, 0, 1], [0, 0, 1], [0, 0, 1], [0, 0, 1], [0, 1, 0], [0.57735026, 0.57735026, 0.57735026], [0, -1, 0]], dtype=np.float32)
+    rays = np.concatenate([rays, np.concatenate([o, d], axis=1)]).astype(np.float32)
+    ref_hits = sc.trace_rays(rays, threads=oracle.hw_threads())
+    tr = tracer_for(sc, karg)
+    try:
+        for strict in (1, 0):
+            tr.set_mode(0, strict)
+            assert_hit_gates(hit_parity(tr.trace_rays(rays), ref_hits), strict)
+        assert tr.dev.stats()["rays"] == len(rays)
+    finally:
+        tr.close()
+
+
+def test_full_size_properties_config1():
+    """BASELINE config 2 at its full size (1920x1080, 100 352 triangles, primary + shadow): size-independent properties.
+    idempotence, strict == fast within the gates, and the union of a 2-way and a 3-way band partition == the whole image."""
+    port = po.PortRaycast() if po.have_port() else best_oracle()
+    sc = port.scene_create([scenes.heightfield(224)])
+    karg = sc.setup(1920, 1080)
+    tr = tracer_for(sc, karg)
+    try:
+        tr.set_mode(1, 0)
+        a = tr.run().copy()
+        b = tr.run().copy()
+        assert np.array_equal(a, b)
+        tr.set_mode(1, 1)
+        s = tr.run().copy()
+        assert channel_diff(a, s) <= 1
+        assert (a != s).mean() <= 1e-4
+        # a bounded sample of rows against the oracle (the whole frame is the bench's job)
+        rows = (500, 508)
+        ref, _ = sc.render(mode=1, rows=rows, threads=port.hw_threads())
+        assert np.array_equal(s[rows[0]:rows[1]], ref[rows[0]:rows[1]])
+        for world in (2, 3):
+            acc = np.zeros_like(a)
+            owner = (np.arange(1080) // 8) % world
+            for rank in range(world):
+                tr.dev.set_partition(rank, world, 8)
+                tr.set_mode(1, 0)
+                canvas = np.zeros_like(a)
+                tr.out.copy_to_dev(canvas)
+                part = tr.run().copy()
+                assert not part[owner != rank].any()          # rows of other ranks untouched
+                acc[owner == rank] = part[owner == rank]
+            assert np.array_equal(acc, a)
+        tr.dev.set_partition(0, 1, 8)
+    finally:
+        tr.close()
+
+
+def test_stats_match_oracle_counters():
+    """strict order visits exactly the nodes/triangles the reference visits: the GPU work counters equal the port's"""
+    if not po.have_port():
+        pytest.skip("C port not built")
+    port = po.PortRaycast()
+    sc = port.scene_create([scenes.heightfield(32), scenes.icosphere((0, 0.4, 0), 0.3, 1, reflectivity=0.5)])
+    karg = sc.setup(128, 96, max_depth=3)
+    _, cnt = sc.render_counted(mode=0, threads=2)
+    tr = tracer_for(sc, karg)
+    try:
+        tr.set_mode(0, 1)
+        tr.dev.enable_stats(True)
+        tr.run()
+        st = tr.dev.stats()
+        for k in ("rays", "box_tests", "tri_tests", "blas_entered", "shaded_hits"):
+            assert st[k] == cnt[k], (k, st[k], cnt[k])
+    finally:
+        tr.close()
+
+
+def test_abi_error_behaviour():
+    """argument checks of the glue layer (reference: runtime/common/callbacks.inc) — non-zero on misuse, 0 on null free"""
+    import ctypes as C
+    L = vx.lib()
+    dev = vx.Device()
+    try:
+        b = C.c_void_p()
+        assert L.vx_mem_alloc(dev.h, 0, 3, C.byref(b)) != 0                 # size 0 rejected
+        assert L.vx_mem_alloc(None, 64, 3, C.byref(b)) != 0                 # null device
+        assert L.vx_mem_free(None) == 0                                     # null buffer frees fine
+        buf = dev.mem_alloc(256)
+        host = np.zeros(512, dtype=np.uint8)
+        assert L.vx_copy_to_dev(buf.h, host.ctypes.data, 0, 512) != 0       # beyond the buffer
+        assert L.vx_copy_to_dev(buf.h, host.ctypes.data, 200, 100) != 0     # offset + size beyond
+        assert L.vx_copy_from_dev(host.ctypes.data, buf.h, 0, 512) != 0
+        assert L.vx_copy_to_dev(buf.h, None, 0, 16) != 0                    # null host pointer
+        src = np.arange(256, dtype=np.uint8)
+        buf.copy_to_dev(src)
+        back = np.zeros(256, dtype=np.uint8)
+        buf.copy_from_dev(back)
+        assert np.array_equal(src, back)
+        a = buf.address
+        assert a >= 0x10000 and a < (1 << 32) and a % 64 == 0               # simx-style address space
+        free0, used0 = dev.mem_info()
+        buf.free()
+        free1, used1 = dev.mem_info()
+        assert used1 < used0 and free1 > free0
+        k = dev.upload_kernel_bytes(vx.DUMMY_KERNEL_IMAGE)                  # reserve at 0x80000000
+        assert k.address == 0x80000000
+        with pytest.raises(vx.VxError):
+            dev.upload_kernel_bytes(vx.DUMMY_KERNEL_IMAGE)                  # same range twice
+        args = dev.upload_bytes(np.zeros(16, dtype=np.uint8))
+        assert L.vx_start(dev.h, k.h, args.h) != 0                          # 16-byte argument block: neither layout
+        assert b"kernel_arg_t" in L.vx_b200_last_error()
+        assert dev.caps(0x3) >= 100 and dev.caps(0x1) == 32                 # NUM_CORES = SMs, NUM_THREADS = warp size
+        v = C.c_uint64()
+        assert L.vx_dev_caps(dev.h, 0x99, C.byref(v)) != 0                  # unknown caps id: error, not abort
+        dev.dcr_write(0x001, 0x1234)
+        assert dev.dcr_read(0x001) == 0x1234
+        assert dev.ready_wait(10) is None                                   # nothing pending
+    finally:
+        dev.close()

@@ -1,0 +1,105 @@
+"""ctypes binding of libvortex-b200-host.so (include/vortex_b200_host.h): host-side scene preparation in the reference's
+layout-A byte formats — what Scene::init / BVH / TLAS / Tracer::setup do in a Vortex raycast host
+(tests/regression/raycast/scene.cpp:17-82, bvh.cpp, tracer.cpp:152-196)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .tracer import KARG_DT, SCENE_BUFFERS
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvortex-b200-host.so")
+EXPORTS = "vxh_scene_create vxh_scene_apply_transform vxh_scene_build vxh_scene_view vxh_scene_free vxh_setup".split()
+
+# defaults of the reference app (raycast/main.cpp:33-42)
+DEFAULT_LIGHT_POS = (0.0, 10.0, -10.0)
+DEFAULT_LIGHT_COLOR = (1.0, 1.0, 1.0)
+DEFAULT_AMBIENT = (0.4, 0.4, 0.4)
+DEFAULT_BACKGROUND = (0.4, 0.35, 0.25)
+
+
+class _View(C.Structure):
+    _fields_ = [(n, t) for name in ("tri", "triEx", "triIdx", "bvh", "blas", "tlas", "tex")
+                for (n, t) in ((name, C.c_void_p), (name + "_bytes", C.c_uint64))] + [("tlas_root", C.c_uint32), ("bvh_nodes_used", C.c_uint32)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `make -C vortex-raytracing_b200/csrc`")
+        L = C.CDLL(LIB_PATH)
+        L.vxh_scene_create.restype = C.c_void_p
+        L.vxh_scene_create.argtypes = [C.c_uint32] + [C.c_void_p] * 8 + [C.c_int]
+        L.vxh_scene_apply_transform.argtypes = [C.c_void_p, C.c_void_p]
+        L.vxh_scene_build.argtypes = [C.c_void_p]
+        L.vxh_scene_view.argtypes = [C.c_void_p, C.POINTER(_View)]
+        L.vxh_scene_free.argtypes = [C.c_void_p]
+        L.vxh_setup.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_int,
+                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        for n in ("vxh_scene_apply_transform", "vxh_scene_build", "vxh_scene_view", "vxh_scene_free", "vxh_setup"):
+            getattr(L, n).restype = None
+        _lib = L
+    return _lib
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+class HostScene:
+    """meshes: list of dict(tris (n,9) f32, triex (n,15) f32, tex (h,w) u32, reflectivity, transform (4,4)|None)."""
+
+    def __init__(self, meshes, threads=0):
+        n = len(meshes)
+        counts = np.array([m["tris"].shape[0] for m in meshes], dtype=np.uint32)
+        tris = np.ascontiguousarray(np.concatenate([m["tris"].reshape(-1, 9) for m in meshes]), dtype=np.float32)
+        triex = np.ascontiguousarray(np.concatenate([m["triex"].reshape(-1, 15) for m in meshes]), dtype=np.float32)
+        tw = np.array([m["tex"].shape[1] for m in meshes], dtype=np.uint32)
+        th = np.array([m["tex"].shape[0] for m in meshes], dtype=np.uint32)
+        texels = np.ascontiguousarray(np.concatenate([m["tex"].reshape(-1) for m in meshes]), dtype=np.uint32)
+        refl = np.array([m.get("reflectivity", 0.0) for m in meshes], dtype=np.float32)
+        tr = None
+        if any(m.get("transform") is not None for m in meshes):
+            tr = np.ascontiguousarray(np.stack([np.asarray(m["transform"], dtype=np.float32) if m.get("transform") is not None
+                                                else np.eye(4, dtype=np.float32) for m in meshes]), dtype=np.float32)
+        self.h = lib().vxh_scene_create(n, counts.ctypes.data, tris.ctypes.data, triex.ctypes.data, tw.ctypes.data, th.ctypes.data,
+                                        texels.ctypes.data, refl.ctypes.data, tr.ctypes.data if tr is not None else None, threads)
+        if not self.h:
+            raise RuntimeError("vxh_scene_create failed")
+        self.karg = None
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().vxh_scene_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def apply_transform(self, m):
+        m = np.ascontiguousarray(np.asarray(m, dtype=np.float32).reshape(16))
+        lib().vxh_scene_apply_transform(self.h, m.ctypes.data)
+
+    def setup(self, width, height, spp=1, max_depth=1, vfov=45.0, zoom=1.0, rotate_scene=True, light_pos=DEFAULT_LIGHT_POS,
+              light_color=DEFAULT_LIGHT_COLOR, ambient=DEFAULT_AMBIENT, background=DEFAULT_BACKGROUND):
+        buf = np.zeros(1, dtype=KARG_DT)
+        lib().vxh_setup(self.h, buf.ctypes.data, width, height, spp, max_depth, vfov, zoom, int(rotate_scene), _f3(light_pos),
+                        _f3(light_color), _f3(ambient), _f3(background))
+        self.karg = buf
+        return buf
+
+    def buffers(self):
+        v = _View()
+        lib().vxh_scene_view(self.h, C.byref(v))
+        out = {}
+        for n in SCENE_BUFFERS:
+            nbytes = getattr(v, n + "_bytes")
+            out[n] = np.frombuffer(C.string_at(getattr(v, n), nbytes), dtype=np.uint8).copy() if nbytes else np.zeros(0, np.uint8)
+        out["tlas_root"] = int(v.tlas_root)
+        out["bvh_nodes_used"] = int(v.bvh_nodes_used)
+        return out

@@ -1,0 +1,86 @@
+"""Screen-space sharding of one frame over the GPUs of a box, one process per GPU.
+
+The image is cut into bands of `band_rows` rows; band j belongs to rank j % world (the same rule the CUDA tile scheduler
+applies after vx_b200_set_partition).  The scene is replicated: every rank uploads the same buffers through vx_copy_to_dev.
+After the render each rank holds its own bands inside a full-size framebuffer; `gather_framebuffer` moves the missing
+bands into rank 0's framebuffer with ONE collective (torch.distributed gather: NCCL over NVLink on the GPU box, gloo in the
+CPU tests) so that the single-buffer vx_copy_from_dev contract of the reference host (raycast/tracer.cpp:239) still holds
+on rank 0.  There is no other data-path communication: rays are independent and the scene is read-only.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def num_bands(height, band_rows=8):
+    return (height + band_rows - 1) // band_rows
+
+
+def band_owner(band, world):
+    return band % world
+
+
+def owned_bands(rank, world, height, band_rows=8):
+    return list(range(rank, num_bands(height, band_rows), world))
+
+
+def owned_rows(rank, world, height, band_rows=8):
+    """row indices rendered by `rank` (ascending)"""
+    y = np.arange(height)
+    return y[(y // band_rows) % world == rank]
+
+
+def rays_per_rank(width, height, world, band_rows=8):
+    return [int(len(owned_rows(r, world, height, band_rows))) * width for r in range(world)]
+
+
+def _padded_view(fb, band_rows, world):
+    """fb [H, W] -> (padded [NBpad, band_rows, W] or a view when no padding is needed, NBpad)"""
+    H, W = fb.shape
+    nb = num_bands(H, band_rows)
+    nb_pad = (nb + world - 1) // world * world
+    if nb_pad * band_rows == H:
+        return fb.view(nb_pad, band_rows, W), nb_pad, False
+    pad = torch.zeros((nb_pad * band_rows, W), dtype=fb.dtype, device=fb.device)
+    pad[:H] = fb
+    return pad.view(nb_pad, band_rows, W), nb_pad, True
+
+
+def gather_framebuffer(fb, rank, world, band_rows=8, group=None, dst=0):
+    """fb: [H, W] int32/uint32-as-int32 tensor (this rank's framebuffer; only its own bands are valid).
+    On return rank `dst`'s fb holds every band.  One gather of H*W*4/world bytes per non-root rank."""
+    if world == 1:
+        return fb
+    H, W = fb.shape
+    bands, nb_pad, padded = _padded_view(fb, band_rows, world)
+    mine = bands[rank::world].contiguous()                       # pack my bands: [NBpad/world, band_rows, W]
+    if rank == dst:
+        recv = [torch.empty_like(mine) for _ in range(world)]
+        dist.gather(mine, gather_list=recv, dst=dst, group=group)
+        if padded:
+            full = torch.empty((nb_pad, band_rows, W), dtype=fb.dtype, device=fb.device)
+            for r in range(world):
+                full[r::world] = recv[r]
+            fb.copy_(full.view(nb_pad * band_rows, W)[:H])
+        else:
+            for r in range(world):
+                if r != rank:
+                    bands[r::world] = recv[r]
+    else:
+        dist.gather(mine, gather_list=None, dst=dst, group=group)
+    return fb
+
+
+class DeviceArray:
+    """Wraps a raw device pointer of the vx arena (vx_b200_device_ptr) as a __cuda_array_interface__ provider so that
+    torch.as_tensor can alias it without a copy (plumbing for NCCL; torch never computes on it)."""
+
+    def __init__(self, ptr, shape, typestr="<i4"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+def framebuffer_tensor(tracer, cuda_device):
+    """the tracer's device framebuffer as a [H, W] int32 torch tensor (alias, no copy)"""
+    arr = DeviceArray(tracer.out.device_ptr, (tracer.height, tracer.width))
+    return torch.as_tensor(arr, device=torch.device("cuda", cuda_device))
