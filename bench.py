@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s of the ray-tracing hot path (BVH traversal + Moller-Trumbore + closest-hit shading) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+One "step" = one frame of the workload through vx_start (+ the NCCL framebuffer gather when N > 1).  Rank 0 prints ONE
+JSON line.  `value` = rays of all ranks / max-over-ranks device time, scene and framebuffer resident in HBM; `e2e` = the same
+frame through the reference-facing call sequence of the raycast host (vx_copy_to_dev of every scene buffer from pinned host
+memory, vx_upload_bytes(kernel_arg_t), vx_start, vx_ready_wait, vx_copy_from_dev of the framebuffer) timed on the host clock.
+`--impl reference` times the reference's own CPU implementation of the same frame (oracle/_ref = the reference sources
+compiled in place; the C port when that library did not travel) on all host threads.
+Workloads are BASELINE.json's configs; rays = every TLASIntersect-equivalent query (primary + shadow + bounce).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: heightfield quads per side, width, height, mode (bit0 shadow, bit1 diffuse bounces), max_depth
+    "cfg1_1080p_primary+shadow_100k": dict(n=224, w=1920, h=1080, mode=1, depth=1, config_index=1),
+    "cfg2_4k_diffuse4_1m": dict(n=708, w=3840, h=2160, mode=2, depth=4, config_index=2),
+    "cfg3_8k_primary+shadow_1m": dict(n=708, w=7680, h=4320, mode=1, depth=1, config_index=3),
+    "primary_4k_1m": dict(n=708, w=3840, h=2160, mode=0, depth=1, config_index=None),
+    "cfg0_cornell64_primary": dict(n=0, w=64, h=64, mode=0, depth=1, config_index=0),
+}
+METRIC = "Mrays/s (primary + shadow + bounce rays, whole job)"
+BAND_ROWS = 8
+
+
+def pkg(name):
+    return importlib.import_module("vortex-raytracing_b200." + name)
+
+
+def make_meshes(wl):
+    scenes = pkg("scenes")
+    return [scenes.cornell_box()] if wl["n"] == 0 else [scenes.heightfield(wl["n"])]
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", float(p.get("sm_max_mhz", 1965.0))
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled while the timed region runs (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def algorithmic_work(st, pixels):
+    """bytes and flops of the REFERENCE algorithm for the counted work (layout A)."""
+    b = 32 * st["box_tests"] + 40 * st["tri_tests"] + 160 * st["blas_entered"] + (60 + 160 + 4) * st["shaded_hits"] + 4 * pixels
+    f = 27 * st["box_tests"] + 53 * st["tri_tests"] + 30 * st["blas_entered"] + 80 * st["shaded_hits"]
+    return b, f
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU legs — the only places this file touches oracle/ (the checker / reported baseline, never the thing shipped)
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_oracle():
+    po = importlib.import_module("oracle.pyoracle")
+    if po.have_ref():
+        return po.RefRaycast(), "reference"
+    if not po.have_port():
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port"], check=True, stdout=subprocess.DEVNULL)
+    return po.PortRaycast(), "port"
+
+
+def cpu_frame_timer(wl, budget_s):
+    """returns (fn() -> (seconds, rays), description).  The sample is the whole frame unless one frame would blow the budget,
+    in which case a centred band of rows (multiple of 8) is timed instead."""
+    orc, kind = cpu_oracle()
+    sc = orc.scene_create(make_meshes(wl))
+    sc.setup(wl["w"], wl["h"], spp=1, max_depth=wl["depth"])
+    threads = orc.hw_threads()
+    H = wl["h"]
+    probe_rows = (H // 2 // 8 * 8, min(H, H // 2 // 8 * 8 + 8))
+    t0 = time.perf_counter()
+    sc.render(mode=wl["mode"], rows=probe_rows, threads=threads)
+    per_row = (time.perf_counter() - t0) / (probe_rows[1] - probe_rows[0])
+    nrows = H if per_row * H <= budget_s else max(8, int(budget_s / per_row) // 8 * 8)
+    y0 = (H - nrows) // 2 // 8 * 8
+    rows = (y0, y0 + nrows)
+
+    def frame():
+        t = time.perf_counter()
+        _, n = sc.render(mode=wl["mode"], rows=rows, threads=threads)
+        dt = time.perf_counter() - t
+        if wl["mode"] == 0:
+            n = (rows[1] - rows[0]) * wl["w"]      # reflectivity 0 in every benchmark scene: one ray per pixel
+        return dt, n
+
+    what = "whole frame" if nrows == H else f"rows {rows[0]}..{rows[1]} of {H}"
+    return frame, kind, threads, f"{what} of {wl['w']}x{wl['h']}, all host threads"
+
+
+def run_reference(args, wl, name):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    frame, kind, threads, sample = cpu_frame_timer(wl, budget_s=max(2.0, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        frame()
+    tot_t, tot_r = 0.0, 0
+    for _ in range(args.steps):
+        dt, n = frame()
+        tot_t += dt
+        tot_r += n
+    v = tot_r / tot_t / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": name, "width": wl["w"], "height": wl["h"], "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32,
+                       "mode": wl["mode"], "max_depth": wl["depth"]},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# the b200 arm
+# ------------------------------------------------------------------------------------------------------------------
+def run_b200(args, wl, name):
+    import torch
+    import torch.distributed as dist
+
+    vx, tracer_mod, host, mg = pkg("vx"), pkg("tracer"), pkg("host"), pkg("multigpu")
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: the b200 backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W, H = wl["w"], wl["h"]
+
+    # ---- host side: scene preparation with the product's own builders (reference byte layouts) ----
+    t0 = time.perf_counter()
+    hs = host.HostScene(make_meshes(wl))
+    karg = hs.setup(W, H, spp=1, max_depth=wl["depth"])
+    bufs = hs.buffers()
+    build_s = time.perf_counter() - t0
+
+    tr = tracer_mod.Tracer(W, H, 1, wl["depth"], cuda_device=local).init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names})
+    tr.dev.set_partition(rank, world, BAND_ROWS)
+    tr.set_mode(wl["mode"], 0)
+    tr._upload_args()
+    ext = torch.cuda.ExternalStream(tr.dev.stream(), device=torch.device("cuda", local))
+    fb = mg.framebuffer_tensor(tr, local)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")       # > 126 MB L2
+
+    def step(timed_events=None):
+        with torch.cuda.stream(ext):
+            flush.zero_()                                       # L2 flush between iterations, outside the timed pair
+            if timed_events:
+                timed_events[0].record()
+            tr.dev.start(tr.krnl, tr.args)                      # vx_start: async, on the same CUDA stream
+            if world > 1:
+                mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
+            if timed_events:
+                timed_events[1].record()
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    sync_all()
+    tr.dev.ready_wait()
+    sampler = ClockSampler(local) if rank == 0 else None
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kernel_ms = []
+    for e in evs:
+        step(e)
+        tr.dev.ready_wait()
+        kernel_ms.append(tr.dev.last_kernel_ms())
+    sync_all()
+    clocks = sampler.stop() if sampler else None
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    st = tr.dev.stats()
+    rays_rank = st["rays"]
+    launches_per_step = st["kernel_launches"]
+    t_ms = torch.tensor([total_ms], dtype=torch.float64, device=f"cuda:{local}")
+    r_cnt = torch.tensor([rays_rank], dtype=torch.int64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(r_cnt, op=dist.ReduceOp.SUM)
+    total_ms, rays_step = float(t_ms.item()), int(r_cnt.item())
+    value = rays_step * args.steps / (total_ms * 1e3)
+
+    # ---- e2e: the raycast host's call sequence with HOST buffers, every step ----
+    pinned = {n: torch.from_numpy(bufs[n].copy()).pin_memory() for n in tracer_mod.SCENE_BUFFERS if bufs[n].nbytes}
+    out_pinned = torch.empty((H, W), dtype=torch.int32).pin_memory()
+    h2d = sum(t.numel() for t in pinned.values()) + 192
+    d2h = W * H * 4 if rank == 0 else 0
+
+    def e2e_step():
+        for n, t in pinned.items():
+            tr.bufs[n].copy_to_dev((t.data_ptr(), t.numel()))
+        tr._upload_args()
+        tr.dev.start(tr.krnl, tr.args)
+        if world > 1:
+            with torch.cuda.stream(ext):
+                mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
+            ext.synchronize()
+        tr.dev.ready_wait()
+        if rank == 0:
+            tr.out.copy_from_dev((out_pinned.data_ptr(), W * H * 4))
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = rays_step * e2e_steps / float(e2e_s.item()) / 1e6
+    e2e_launches = tr.dev.stats()["kernel_launches"]
+
+    # ---- roofline of the dominant kernel (k_render_a): algorithmic bytes of the reference algorithm / kernel time ----
+    tr.set_mode(wl["mode"], 1)              # strict order = the reference's own visiting order => its algorithmic work
+    tr.dev.enable_stats(True)
+    tr._upload_args()
+    tr.launch()
+    work = tr.dev.stats()
+    tr.dev.enable_stats(False)
+    tr.set_mode(wl["mode"], 0)
+    pixels_rank = len(mg.owned_rows(rank, world, H, BAND_ROWS)) * W
+    abytes, aflops = algorithmic_work(work, pixels_rank)
+    k_ms = float(np.mean(kernel_ms))
+    hbm, hbm_src, sm_mhz = peaks()
+    achieved = abytes / (k_ms * 1e-3) / 1e9
+    nsm = tr.dev.caps(0x3)
+    fp32_peak = nsm * 128 * 2 * sm_mhz * 1e6 / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(name)
+        except Exception:
+            traffic = None
+
+    extra = {}
+    if rank == 0 and world == 1 and args.extra:
+        tr.close()
+        tr = None
+        for other in ("primary_4k_1m", "cfg2_4k_diffuse4_1m"):
+            if other != name:
+                extra[other] = quick_run(other, local)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        frame, kind, threads, sample = cpu_frame_timer(wl, budget_s=20.0)
+        best = None
+        for _ in range(2):
+            dt, n = frame()
+            best = (dt, n) if best is None or dt < best[0] else best
+        cpu = {"value": best[1] / best[0] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample + ", best of 2"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": name, "baseline_config_index": wl["config_index"], "width": W, "height": H,
+                           "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32, "mode": wl["mode"], "max_depth": wl["depth"],
+                           "rays_per_step": rays_step, "partition": f"{BAND_ROWS}-row bands round-robin over {world} GPU(s), scene replicated",
+                           "l2": "512 MB memset between timed iterations (L2 flush); timed per step with CUDA events on the launch stream",
+                           "host_bvh_build_s": round(build_s, 3), "extra_workloads": extra},
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                        "timer": "host wall clock around the synchronous vx_* calls, max over ranks", "launches_per_step": e2e_launches},
+                "gpu_launches": int(launches_per_step) * args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
+                             "peak_source": hbm_src, "kernel": "k_render_a", "kernel_ms": k_ms,
+                             "algorithmic_bytes_per_launch": abytes, "algorithmic_bytes_per_ray": abytes / max(1, work["rays"]),
+                             "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
+                                      "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},
+                             "work_per_ray": {k: work[k] / max(1, work["rays"]) for k in ("box_tests", "tri_tests", "blas_entered", "shaded_hits")}},
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if tr is not None:
+        tr.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def quick_run(name, local, steps=5):
+    """kernel-only Mrays/s of another workload on one GPU (reported under config.extra_workloads; not the headline)."""
+    tracer_mod, host = pkg("tracer"), pkg("host")
+    wl = WORKLOADS[name]
+    hs = host.HostScene(make_meshes(wl))
+    karg = hs.setup(wl["w"], wl["h"], spp=1, max_depth=wl["depth"])
+    tr = tracer_mod.Tracer(wl["w"], wl["h"], 1, wl["depth"], cuda_device=local).init(hs.buffers())
+    tr.setup({k: karg[k][0] for k in karg.dtype.names})
+    tr.set_mode(wl["mode"], 0)
+    tr._upload_args()
+    ms = []
+    for i in range(steps + 3):
+        tr.launch()
+        if i >= 3:
+            ms.append(tr.dev.last_kernel_ms())
+    rays = tr.dev.stats()["rays"]
+    tr.close()
+    return {"mrays_per_s": rays / (float(np.mean(ms)) * 1e3), "kernel_ms": float(np.mean(ms)), "rays_per_step": rays,
+            "note": "kernel time only, L2 not flushed (working set > L2 for the 1M-triangle scenes' framebuffer+scene)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--extra", type=int, default=1, help="also report kernel-only numbers of the 1M-triangle workloads (N=1)")
+    args = ap.parse_args()
+    name = args.workload or ("cfg1_1080p_primary+shadow_100k" if args.gpus == 1 else "cfg3_8k_primary+shadow_1m")
+    wl = WORKLOADS[name]
+    if args.impl == "reference":
+        run_reference(args, wl, name)
+    else:
+        run_b200(args, wl, name)
+
+
+if __name__ == "__main__":
+    main()
