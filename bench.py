@@ -188,7 +188,7 @@ def run_b200(args, wl, name):
     tr = tracer_mod.Tracer(W, H, 1, wl["depth"], cuda_device=local).init(bufs)
     tr.setup({k: karg[k][0] for k in karg.dtype.names})
     tr.dev.set_partition(rank, world, BAND_ROWS)
-    tr.set_mode(wl["mode"], 0)
+    tr.set_mode(wl["mode"], 0, kernel=args.kernel)
     tr._upload_args()
     ext = torch.cuda.ExternalStream(tr.dev.stream(), device=torch.device("cuda", local))
     fb = mg.framebuffer_tensor(tr, local)
@@ -297,7 +297,7 @@ def run_b200(args, wl, name):
         tr = None
         for other in ("primary_4k_1m", "cfg2_4k_diffuse4_1m"):
             if other != name:
-                extra[other] = quick_run(other, local)
+                extra[other] = quick_run(other, local, kernel=args.kernel)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -322,7 +322,7 @@ def run_b200(args, wl, name):
                         "timer": "host wall clock around the synchronous vx_* calls, max over ranks", "launches_per_step": e2e_launches},
                 "gpu_launches": int(launches_per_step) * args.steps,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
-                             "peak_source": hbm_src, "kernel": "k_render_a", "kernel_ms": k_ms,
+                             "peak_source": hbm_src, "kernel": "k_render_a" if args.kernel == 1 else "k_render_m", "kernel_ms": k_ms,
                              "algorithmic_bytes_per_launch": abytes, "algorithmic_bytes_per_ray": abytes / max(1, work["rays"]),
                              "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
                                       "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},
@@ -336,7 +336,7 @@ def run_b200(args, wl, name):
         dist.destroy_process_group()
 
 
-def quick_run(name, local, steps=5):
+def quick_run(name, local, steps=5, kernel=0):
     """kernel-only Mrays/s of another workload on one GPU (reported under config.extra_workloads; not the headline)."""
     tracer_mod, host = pkg("tracer"), pkg("host")
     wl = WORKLOADS[name]
@@ -344,7 +344,7 @@ def quick_run(name, local, steps=5):
     karg = hs.setup(wl["w"], wl["h"], spp=1, max_depth=wl["depth"])
     tr = tracer_mod.Tracer(wl["w"], wl["h"], 1, wl["depth"], cuda_device=local).init(hs.buffers())
     tr.setup({k: karg[k][0] for k in karg.dtype.names})
-    tr.set_mode(wl["mode"], 0)
+    tr.set_mode(wl["mode"], 0, kernel=kernel)
     tr._upload_args()
     ms = []
     for i in range(steps + 3):
@@ -365,6 +365,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--kernel", type=int, default=0, help="layout-A render kernel: 0 = ray state machine (default), 1 = one pixel per lane")
     ap.add_argument("--extra", type=int, default=1, help="also report kernel-only numbers of the 1M-triangle workloads (N=1)")
     args = ap.parse_args()
     name = args.workload or ("cfg1_1080p_primary+shadow_100k" if args.gpus == 1 else "cfg3_8k_primary+shadow_1m")

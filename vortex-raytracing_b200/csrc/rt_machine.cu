@@ -1,0 +1,466 @@
+// rt_machine.cu — the layout-A render kernel as a persistent, warp-scheduled ray state machine (sm_100a).
+//
+// Why: ncu on the one-pixel-per-lane kernel (profiles/r01_*) shows 5.5-8.8 active threads per warp instruction: rays of one
+// warp finish at very different times (silhouettes, grazing rays, any-hit shadow rays) and inner-node, leaf and shading code
+// serialise against each other.  Here every lane owns a ray *slot*; a warp repeatedly runs the one operation most of its
+// lanes are waiting for:
+//     GEN   empty lanes pull the next pixels from the tile counter (ballot-ranked, so the warp stays compact)
+//     TRAV  while-while traversal: all lanes descend inner nodes together; leaves/instance entries are postponed until fewer
+//           than kInnerQuorum lanes still have an inner node, then tested together
+//     POST  lanes whose traversal finished shade their hit (or resolve their shadow ray) and either queue the next ray of the
+//           path in the same slot (shadow ray, mirror/diffuse bounce, next sample) or write the pixel and become empty
+// Path state that must survive a traversal (accumulated colour, throughput, RNG seed, the saved shading context of a
+// shadow ray, the world-space ray while inside an instance) lives in shared memory, one word column per thread; registers
+// hold only the traversal state.  Per-ray arithmetic is unchanged from rt_raycast.cu — same slab and Moller-Trumbore
+// expressions, same shading expressions, -fmad=false — so strict order stays bit-identical to the reference
+// (tests/regression/raycast/render.h:74-276) and fast order differs from it only in equal-t ties.
+#include "rt_device.cuh"
+
+namespace vxb {
+namespace {
+using namespace dev;
+
+constexpr uint32_t kTlasTag = 0x80000000u;   // stack entry / cursor: payload is a TLAS node index
+constexpr uint32_t kKindShift = 27;          // bits 27..30: 0 = inner node pair, 1..14 = leaf with that many triangles, 15 = read the node
+constexpr uint32_t kPay = (1u << kKindShift) - 1;
+constexpr uint32_t kReadNode = 15u;
+
+constexpr uint32_t S_EMPTY = 0, S_TRAV = 1, S_DONE = 2, S_MASK = 3;
+constexpr uint32_t F_ANY = 4, F_NAN = 8, F_INBLAS = 16, F_OCCL = 32;
+
+constexpr uint32_t kRefillQuorum = 20;   // run GEN/POST when fewer lanes than this are traversing
+constexpr uint32_t kInnerQuorum = 8;     // leave the inner-node loop when fewer lanes than this have an inner node
+constexpr uint32_t kChunk = 256;         // pixels a warp reserves per atomic
+
+// shared-memory columns (one 32-bit word per thread each)
+enum : uint32_t {
+  C_PIX, C_COLX, C_COLY, C_COLZ, C_RADX, C_RADY, C_RADZ, C_THRX, C_THRY, C_THRZ, C_SEED, C_PACK,   // PACK: bounce | sample<<8 | stage<<31
+  C_WOX, C_WOY, C_WOZ, C_WDX, C_WDY, C_WDZ,                                                         // world-space ray of the slot
+  C_BASE_END,
+  C_TEXX = C_BASE_END, C_TEXY, C_TEXZ, C_ATT, C_NDL, C_NX, C_NY, C_NZ, C_IX, C_IY, C_IZ, C_REFL, C_PDX, C_PDY, C_PDZ,   // shadow continuation
+  C_SHADOW_END
+};
+
+struct Lane {
+  f3 o, d, id;          // active ray (world space at TLAS level, object space inside an instance) and its reciprocal direction
+  float dist, bx, by;   // closest hit so far
+  uint32_t hblas, htri;
+  uint32_t cur, sp, st;
+  uint32_t node_base, blas;
+};
+
+__device__ __forceinline__ uint32_t enc_child(uint32_t leftFirst, uint32_t triCount, uint32_t nodeIdx) {
+  if (triCount < kReadNode && leftFirst <= kPay) return (triCount << kKindShift) | leftFirst;
+  return (kReadNode << kKindShift) | nodeIdx;
+}
+
+__device__ __forceinline__ void set_recip(Lane &L) {
+  L.id = mk3(1.0f / L.d.x, 1.0f / L.d.y, 1.0f / L.d.z);
+  bool bad = isinf(L.id.x) || isinf(L.id.y) || isinf(L.id.z) || isnan(L.id.x) || isnan(L.id.y) || isnan(L.id.z);
+  L.st = bad ? (L.st | F_NAN) : (L.st & ~F_NAN);
+}
+
+struct Smem {
+  float *base;
+  uint32_t tid;
+  __device__ __forceinline__ float &f(uint32_t col) const { return base[col * kBlockThreads + tid]; }
+  __device__ __forceinline__ uint32_t &u(uint32_t col) const { return reinterpret_cast<uint32_t *>(base)[col * kBlockThreads + tid]; }
+  __device__ __forceinline__ f3 get3(uint32_t col) const { return mk3(f(col), f(col + 1), f(col + 2)); }
+  __device__ __forceinline__ void put3(uint32_t col, f3 v) const { f(col) = v.x, f(col + 1) = v.y, f(col + 2) = v.z; }
+};
+
+// queue a ray in this lane's slot: TLASIntersect entry (render.h:143-153)
+__device__ __forceinline__ void start_ray(Lane &L, const Smem &sm, const SceneA &sc, f3 o, f3 d, float tmax, bool any, Local &lc) {
+  sm.put3(C_WOX, o);
+  sm.put3(C_WDX, d);
+  L.o = o, L.d = d;
+  L.st = S_TRAV | (any ? F_ANY : 0u);
+  set_recip(L);
+  L.dist = tmax, L.bx = 0.f, L.by = 0.f, L.hblas = 0, L.htri = 0;
+  L.cur = kTlasTag | sc.tlas_root;
+  L.sp = 0;
+  lc.rays++;
+}
+
+template <bool STRICT>
+__device__ __forceinline__ void pop(Lane &L, const uint32_t *stk_e, const float *stk_d) {
+  if (STRICT) {   // the reference never re-tests a pushed node (render.h:82-83, :151-152)
+    if (L.sp == 0) { L.st = (L.st & ~S_MASK) | S_DONE; return; }
+    L.cur = stk_e[--L.sp];
+  } else {
+    for (;;) {
+      if (L.sp == 0) { L.st = (L.st & ~S_MASK) | S_DONE; return; }
+      --L.sp;
+      if (stk_d[L.sp] < L.dist) { L.cur = stk_e[L.sp]; return; }
+    }
+  }
+}
+
+// one inner-node visit inside an instance: both children are one 64-byte record (render.h:100-124)
+template <bool STRICT, bool STATS>
+__device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool careful, uint32_t *stk_e, float *stk_d, Local &lc) {
+  uint32_t first = L.cur & kPay;
+  const uint8_t *pair = sc.nodes + ((size_t)L.node_base + first) * sizeof(BvhNodeA);
+  float4 l0 = ldg4(pair), l1 = ldg4(pair + 16), r0 = ldg4(pair + 32), r1 = ldg4(pair + 48);
+  float dL = slab(l0, l1, L.o, L.id, careful);
+  float dR = slab(r0, r1, L.o, L.id, careful);
+  if (STATS) lc.box += 2;
+  bool hitL = (dL != kLargeFloat) && (dL < L.dist);
+  bool hitR = (dR != kLargeFloat) && (dR < L.dist);
+  uint32_t eL = enc_child(__float_as_uint(l0.w), __float_as_uint(l1.w), first);
+  uint32_t eR = enc_child(__float_as_uint(r0.w), __float_as_uint(r1.w), first + 1);
+  if (hitL && hitR) {
+    bool right_next = STRICT ? (dL < dR) : (dR < dL);   // STRICT: the reference visits the FARTHER child first (render.h:113-118)
+    stk_e[L.sp] = right_next ? eL : eR;
+    if (!STRICT) stk_d[L.sp] = right_next ? dL : dR;
+    ++L.sp;
+    L.cur = right_next ? eR : eL;
+  } else if (hitL) {
+    L.cur = eL;
+  } else if (hitR) {
+    L.cur = eR;
+  } else {
+    pop<STRICT>(L, stk_e, stk_d);
+  }
+}
+
+// everything that is not an inner-node pair: leaves, nodes that must be read first, TLAS nodes / instance entry
+template <bool STRICT, bool STATS>
+__device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA &sc, uint32_t *stk_e, float *stk_d, Local &lc) {
+  if (L.cur & kTlasTag) {
+    if (L.st & F_INBLAS) {   // back from an instance: the active ray becomes the world-space ray again
+      L.o = sm.get3(C_WOX), L.d = sm.get3(C_WDX);
+      L.st &= ~F_INBLAS;
+      set_recip(L);
+    }
+    const uint8_t *n = reinterpret_cast<const uint8_t *>(sc.tlas + (L.cur & kPay));
+    float4 a = ldg4(n), b = ldg4(n + 16);
+    uint32_t leftRight = __float_as_uint(a.w);
+    if (leftRight == 0) {
+      // BLASIntersect (render.h:128-141): ray_t::transform = direction (w=0) then origin (w=1), not renormalised
+      uint32_t bi = __float_as_uint(b.w);
+      const BlasNodeA *blas = sc.blas + bi;
+      float M[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) M[i] = __ldg(blas->invTransform + i);
+      f3 od = xform_vec(L.d, M), oo = xform_pos(L.o, M);
+      L.d = od, L.o = oo;
+      L.st |= F_INBLAS;
+      set_recip(L);
+      L.node_base = __ldg(&blas->bvh_offset);
+      L.blas = bi;
+      L.cur = kReadNode << kKindShift;   // node 0 of the instance
+      if (STATS) lc.blas++;
+    } else {
+      uint32_t left = leftRight & 0xFFFFu, right = leftRight >> 16;
+      const uint8_t *pl = reinterpret_cast<const uint8_t *>(sc.tlas + left);
+      const uint8_t *pr = reinterpret_cast<const uint8_t *>(sc.tlas + right);
+      bool careful = (L.st & F_NAN) != 0;
+      float dL = slab(ldg4(pl), ldg4(pl + 16), L.o, L.id, careful);
+      float dR = slab(ldg4(pr), ldg4(pr + 16), L.o, L.id, careful);
+      if (STATS) lc.box += 2;
+      bool hitL = (dL != kLargeFloat) && (dL < L.dist);
+      bool hitR = (dR != kLargeFloat) && (dR < L.dist);
+      if (hitL && hitR) {   // near child first at this level (render.h:175-180)
+        bool swap = dL > dR;
+        stk_e[L.sp] = kTlasTag | (swap ? left : right);
+        if (!STRICT) stk_d[L.sp] = swap ? dL : dR;
+        ++L.sp;
+        L.cur = kTlasTag | (swap ? right : left);
+      } else if (hitL) {
+        L.cur = kTlasTag | left;
+      } else if (hitR) {
+        L.cur = kTlasTag | right;
+      } else {
+        pop<STRICT>(L, stk_e, stk_d);
+      }
+    }
+    return;
+  }
+  uint32_t kind = (L.cur >> kKindShift) & 15u, first = L.cur & kPay, count = kind;
+  if (kind == kReadNode) {
+    const uint8_t *n = sc.nodes + ((size_t)L.node_base + first) * sizeof(BvhNodeA);
+    float4 a = ldg4(n), b = ldg4(n + 16);
+    first = __float_as_uint(a.w);
+    count = __float_as_uint(b.w);
+    if (count == 0) {   // an inner node after all: its child pair is visited by the inner loop
+      L.cur = first & kPay;
+      return;
+    }
+  }
+  const GpuTri *tp = sc.gtri + first;
+  Ray r{L.o, L.d};
+  for (uint32_t i = 0; i < count; ++i) {
+    const uint8_t *q = reinterpret_cast<const uint8_t *>(tp + i);
+    float4 q0 = ldg4(q), q1 = ldg4(q + 16), q2 = ldg4(q + 32);
+    float t, w1, w2;
+    if (STATS) lc.tri++;
+    if (moller_trumbore(r, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), mk3(q2.x, q2.y, q2.z), t, w1, w2) && t < L.dist) {
+      L.dist = t;
+      if (L.st & F_ANY) {   // shadow ray: any accepted hit below tmax decides
+        L.st = (L.st & ~S_MASK) | S_DONE | F_OCCL;
+        return;
+      }
+      L.bx = w1, L.by = w2;
+      L.hblas = L.blas;
+      L.htri = __float_as_uint(q0.w);
+    }
+  }
+  pop<STRICT>(L, stk_e, stk_d);
+}
+
+__device__ __forceinline__ bool is_inner(const Lane &L) { return (L.st & S_MASK) == S_TRAV && (L.cur >> kKindShift) == 0u; }
+
+// TRAV: runs until fewer than `quorum` lanes of the warp are still traversing
+template <bool STRICT, bool STATS>
+__device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &sc, uint32_t quorum, uint32_t inner_quorum, uint32_t *stk_e,
+                                         float *stk_d, Local &lc) {
+  for (;;) {
+    for (;;) {
+      bool inner = is_inner(L);
+      unsigned m = __ballot_sync(0xffffffffu, inner);
+      if ((uint32_t)__popc(m) < inner_quorum) break;
+      bool careful = __any_sync(0xffffffffu, inner && (L.st & F_NAN));   // warp-uniform: no divergence on the NaN-exact min/max path
+      if (inner) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);
+    }
+    if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
+    unsigned t = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
+    if ((uint32_t)__popc(t) < quorum) return;
+  }
+}
+
+struct Frame {   // warp-uniform view of the launch
+  uint32_t W, H, spp, max_depth;
+  uint32_t tcols, tiles_per_band, band_rows, world, rank;
+  uint32_t total;   // work items (pixel slots of whole 8x4 tiles) of this rank
+};
+
+// begin sample `s` of pixel `pix`: GenerateRay + the per-sample seed of the extended modes (tracer.cpp:254-257)
+template <uint32_t MODE>
+__device__ __forceinline__ void begin_sample(Lane &L, const Smem &sm, const RenderA &p, uint32_t pix, uint32_t s, Local &lc) {
+  const KernelArgA &a = p.arg;
+  sm.put3(C_RADX, mk3(0, 0, 0));
+  sm.put3(C_THRX, mk3(1, 1, 1));
+  sm.u(C_PACK) = (s << 8);   // bounce 0, stage = closest
+  if (MODE != 0) {
+    uint32_t seed = wang_hash(pix * a.samples_per_pixel + s + 1);
+    sm.u(C_SEED) = seed ? seed : 1u;
+  }
+  Ray r = generate_ray(pix % a.dst_width, pix / a.dst_width, a);
+  start_ray(L, sm, p.scene, r.o, r.d, kLargeFloat, false, lc);
+}
+
+// POST: closest-hit shading / shadow resolution and the bounce loop of Trace (render.h:210-276) and of the extended
+// modes (shadow rays, diffuse bounces; same expressions as rt_raycast.cu:trace_ext and the CPU oracles' TraceExt)
+template <uint32_t MODE, bool STATS>
+__device__ __forceinline__ void post(Lane &L, const Smem &sm, const RenderA &p, Local &lc) {
+  constexpr bool SHADOW = (MODE & 1u) != 0, DIFFUSE = (MODE & 2u) != 0;
+  const KernelArgA &a = p.arg;
+  const f3 light_pos = mk3(a.light_pos.x, a.light_pos.y, a.light_pos.z);
+  const f3 light_color = mk3(a.light_color.x, a.light_color.y, a.light_color.z);
+  const f3 ambient = mk3(a.ambient_color.x, a.ambient_color.y, a.ambient_color.z);
+  const f3 background = mk3(a.background_color.x, a.background_color.y, a.background_color.z);
+  uint32_t pack = sm.u(C_PACK);
+  uint32_t bounce = pack & 255u, sample = (pack >> 8) & 0x7FFFFFu;
+  bool shadow_stage = SHADOW && (pack >> 31);
+  f3 radiance = sm.get3(C_RADX), thr = sm.get3(C_THRX);
+  f3 texColor, N, I, prev_d;
+  float att, NdotL, refl;
+  bool end_path = false;
+  if (shadow_stage) {
+    texColor = sm.get3(C_TEXX), N = sm.get3(C_NX), I = sm.get3(C_IX), prev_d = sm.get3(C_PDX);
+    att = sm.f(C_ATT), NdotL = sm.f(C_NDL), refl = sm.f(C_REFL);
+    if (L.st & F_OCCL) NdotL = 0.0f;
+  } else {
+    if (L.dist == kLargeFloat) {
+      radiance = radiance + background * thr;
+      end_path = true;
+    } else {
+      if (STATS) lc.shaded++;
+      Ray wr{sm.get3(C_WOX), sm.get3(C_WDX)};
+      Hit h{L.dist, L.bx, L.by, 1 - L.bx - L.by, L.hblas, L.htri};
+      Surface s = surface_at(p.scene, wr, h);
+      texColor = s.texColor, N = s.N, I = s.I, refl = s.reflectivity, prev_d = wr.d;
+      f3 Lv = light_pos - I;                       // diffuseLighting (render.h:58-70)
+      float dist = length3(Lv);
+      Lv = Lv * (1.0f / dist);
+      att = 1.0f / (1.0f + dist * 0.1f);
+      NdotL = std_max(0.0f, dot3(N, Lv));
+      if (SHADOW && NdotL > 0.0f) {
+        f3 Ns = (dot3(N, prev_d) > 0.0f) ? neg(N) : N;
+        f3 O = I + Ns * 0.001f;
+        f3 Sv = light_pos - O;
+        float d2 = length3(Sv);
+        f3 D = Sv * (1.0f / d2);
+        sm.put3(C_TEXX, texColor), sm.put3(C_NX, N), sm.put3(C_IX, I), sm.put3(C_PDX, prev_d);
+        sm.f(C_ATT) = att, sm.f(C_NDL) = NdotL, sm.f(C_REFL) = refl;
+        sm.u(C_PACK) = pack | 0x80000000u;
+        start_ray(L, sm, p.scene, O, D, d2, true, lc);
+        return;
+      }
+    }
+  }
+  if (!end_path) {
+    f3 diffuse = texColor * (ambient + att * light_color * NdotL);
+    if (DIFFUSE) {
+      radiance = radiance + thr * diffuse;
+      thr = thr * texColor;
+      if (bounce + 1 < a.max_depth) {
+        uint32_t seed = sm.u(C_SEED);
+        float px, py, pz, l2;
+        do {
+          px = random_float(seed) * 2.0f - 1.0f;
+          py = random_float(seed) * 2.0f - 1.0f;
+          pz = random_float(seed) * 2.0f - 1.0f;
+          l2 = px * px + py * py + pz * pz;
+        } while (l2 > 1.0f || l2 < 1e-6f);
+        sm.u(C_SEED) = seed;
+        float il = 1.0f / sqrtf(l2);
+        f3 Ns = (dot3(N, prev_d) > 0.0f) ? neg(N) : N;
+        f3 O = I + Ns * 0.001f;
+        f3 D = Ns + mk3(px * il, py * il, pz * il);
+        float dl2 = dot3(D, D);
+        if (dl2 < 1e-12f) D = Ns;
+        else D = D * (1.0f / sqrtf(dl2));
+        sm.put3(C_RADX, radiance), sm.put3(C_THRX, thr);
+        sm.u(C_PACK) = (sample << 8) | (bounce + 1);
+        start_ray(L, sm, p.scene, O, D, kLargeFloat, false, lc);
+        return;
+      }
+    } else {
+      radiance = radiance + thr * diffuse * (1 - refl);
+      thr = thr * refl;
+      if (refl > 0.0f && bounce + 1 < a.max_depth) {
+        f3 R = normalize3(prev_d - 2.0f * N * dot3(N, prev_d));
+        sm.put3(C_RADX, radiance), sm.put3(C_THRX, thr);
+        sm.u(C_PACK) = (sample << 8) | (bounce + 1);
+        start_ray(L, sm, p.scene, I + R * 0.001f, R, kLargeFloat, false, lc);
+        return;
+      }
+      radiance = radiance + thr * background;
+    }
+  }
+  // end of this sample: color += Trace(...) (tracer.cpp:255-258); no jitter, no division by spp
+  uint32_t pix = sm.u(C_PIX);
+  f3 color = sm.get3(C_COLX) + radiance;
+  if (sample + 1 < a.samples_per_pixel) {
+    sm.put3(C_COLX, color);
+    begin_sample<MODE>(L, sm, p, pix, sample + 1, lc);
+    return;
+  }
+  p.out[pix] = rgb32f_to_rgb8(color);
+  L.st = S_EMPTY;
+}
+
+template <uint32_t MODE, bool STRICT, bool STATS>
+__global__ void __launch_bounds__(kBlockThreads) k_render_m(const __grid_constant__ RenderA p) {
+  constexpr uint32_t kCols = (MODE & 1u) ? C_SHADOW_END : C_BASE_END;
+  __shared__ float s_cols[kCols * kBlockThreads];
+  uint32_t stk_e[kStackSize];
+  float stk_d[kStackSize];
+  const Smem sm{s_cols, threadIdx.x};
+  const KernelArgA &a = p.arg;
+  const uint32_t lane = threadIdx.x & 31;
+  Frame f;
+  f.W = a.dst_width, f.H = a.dst_height;
+  f.tcols = (f.W + kTileW - 1) / kTileW;
+  f.band_rows = p.part.band_rows, f.world = p.part.world, f.rank = p.part.rank;
+  const uint32_t nbands_total = (f.H + f.band_rows - 1) / f.band_rows;
+  const uint32_t nbands = nbands_total > f.rank ? (nbands_total - f.rank + f.world - 1) / f.world : 0;
+  f.tiles_per_band = (f.band_rows / kTileH) * f.tcols;
+  f.total = nbands * f.tiles_per_band * 32u;
+
+  Lane L;
+  L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.node_base = 0, L.blas = 0;
+  L.o = L.d = L.id = mk3(0, 0, 0);
+  Local lc{0, 0, 0, 0, 0};
+  uint32_t chunk_next = 0, chunk_end = 0;
+  bool exhausted = (f.total == 0);
+
+  for (;;) {
+    unsigned trav = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
+    unsigned done = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_DONE);
+    const uint32_t quorum = exhausted ? 1u : kRefillQuorum;
+    if (trav && ((uint32_t)__popc(trav) >= quorum || (!done && exhausted))) {
+      traverse<STRICT, STATS>(L, sm, p.scene, quorum, exhausted ? 1u : kInnerQuorum, stk_e, stk_d, lc);
+      continue;
+    }
+    if (done) {
+      if ((L.st & S_MASK) == S_DONE) post<MODE, STATS>(L, sm, p, lc);
+      continue;   // POST may have queued follow-up rays; re-evaluate before pulling new pixels
+    }
+    if (exhausted) {
+      if (!trav) break;
+      continue;
+    }
+    // GEN: empty lanes take the next pixels of the warp's chunk, compactly (ballot rank)
+    unsigned need = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_EMPTY);
+    while (need) {
+      if (chunk_next == chunk_end) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(p.tile_counter, kChunk);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= f.total) {
+          exhausted = true;
+          break;
+        }
+        chunk_next = base;
+        chunk_end = min(base + kChunk, f.total);
+      }
+      uint32_t avail = chunk_end - chunk_next;
+      bool mine = (need >> lane) & 1u;
+      uint32_t my_rank = __popc(need & ((1u << lane) - 1u));
+      bool take = mine && my_rank < avail;
+      if (take) {
+        uint32_t item = chunk_next + my_rank;
+        uint32_t tile = item >> 5, in_tile = item & 31u;
+        uint32_t band_local = tile / f.tiles_per_band, r = tile % f.tiles_per_band;
+        uint32_t trow = r / f.tcols, tcol = r % f.tcols;
+        uint32_t x = tcol * kTileW + (in_tile & (kTileW - 1));
+        uint32_t y = (band_local * f.world + f.rank) * f.band_rows + trow * kTileH + (in_tile / kTileW);
+        if (x < f.W && y < f.H) {
+          uint32_t pix = y * f.W + x;
+          sm.u(C_PIX) = pix;
+          sm.put3(C_COLX, mk3(0, 0, 0));
+          begin_sample<MODE>(L, sm, p, pix, 0, lc);
+        }
+      }
+      unsigned took = __ballot_sync(0xffffffffu, take);
+      chunk_next += (uint32_t)__popc(took);
+      need &= ~took;
+    }
+  }
+  __syncwarp();
+  flush_counters(p.counters, lc, STATS);
+}
+
+template <uint32_t MODE, bool STRICT, bool STATS>
+int launch_m(const RenderA &p, int num_sms, cudaStream_t stream) {
+  auto kern = k_render_m<MODE, STRICT, STATS>;
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, 0);
+  if (e != cudaSuccess) return -(int)e;
+  if (per_sm < 1) per_sm = 1;
+  kern<<<num_sms * per_sm, kBlockThreads, 0, stream>>>(p);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? 1 : -(int)e;
+}
+
+template <bool STRICT, bool STATS>
+int launch_mm(const RenderA &p, int num_sms, cudaStream_t stream) {
+  switch (p.mode & 3u) {
+    case 0: return launch_m<0, STRICT, STATS>(p, num_sms, stream);
+    case 1: return launch_m<1, STRICT, STATS>(p, num_sms, stream);
+    case 2: return launch_m<2, STRICT, STATS>(p, num_sms, stream);
+    default: return launch_m<3, STRICT, STATS>(p, num_sms, stream);
+  }
+}
+
+}  // namespace
+
+int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
+  if (p.strict_order) return p.stats ? launch_mm<true, true>(p, num_sms, stream) : launch_mm<true, false>(p, num_sms, stream);
+  return p.stats ? launch_mm<false, true>(p, num_sms, stream) : launch_mm<false, false>(p, num_sms, stream);
+}
+
+}  // namespace vxb

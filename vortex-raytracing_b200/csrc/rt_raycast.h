@@ -53,5 +53,8 @@ cudaError_t launch_gather_tris(const TriA *tri, const uint32_t *triIdx, GpuTri *
 // returns the number of kernels launched (>0) or a negative cudaError_t
 int launch_render_a(const RenderA &p, int num_sms, cudaStream_t stream);
 int launch_trace_a(const TraceA &p, int num_sms, cudaStream_t stream);
+// the warp-scheduled ray state machine (rt_machine.cu); scenes must have < 2^27 BVH nodes (else use launch_render_a)
+int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream);
+constexpr uint64_t kMachineMaxNodes = 1ull << 27;
 
 }  // namespace vxb

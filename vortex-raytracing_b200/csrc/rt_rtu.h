@@ -7,7 +7,9 @@
 // b200-private DCR: which primary-ray generator the layout-B kernel uses.
 //   0 = the hard-coded Sponza camera of tests/regression/raytracing/kernel.cpp:28-39 (what the reference runs)
 //   1 = the kernel_arg_t pinhole camera (render.h-style GenerateRay), for scenes that are not Sponza
+#ifndef VX_DCR_B200_RT_CAMERA
 #define VX_DCR_B200_RT_CAMERA 0x0F3
+#endif
 
 namespace vxb {
 

@@ -421,7 +421,11 @@ private:
       p.scene = sc, p.arg = a, p.out = out, p.part = part_;
       p.mode = dcr_get(VX_DCR_B200_RT_MODE), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
       p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
-      rc = launch_render_a(p, prop_.multiProcessorCount, stream_);
+      uint64_t bvh_bytes = 0;
+      const uint8_t *dummy = nullptr;
+      resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &dummy, &bvh_bytes);
+      bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes;
+      rc = simple ? launch_render_a(p, prop_.multiProcessorCount, stream_) : launch_render_machine(p, prop_.multiProcessorCount, stream_);
     } else {
       TraceA p{};
       p.scene = sc, p.arg = a, p.rays = rays, p.count = count, p.hits = hits;

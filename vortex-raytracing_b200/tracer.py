@@ -114,9 +114,11 @@ class Tracer:
             rb.free()
         return out
 
-    def set_mode(self, mode=0, strict_order=False):
+    def set_mode(self, mode=0, strict_order=False, kernel=None):
         self.dev.dcr_write(vx.VX_DCR_B200_RT_MODE, int(mode))
         self.dev.dcr_write(vx.VX_DCR_B200_RT_ORDER, int(bool(strict_order)))
+        if kernel is not None:   # 0 = ray state machine (default), 1 = one pixel per lane
+            self.dev.dcr_write(vx.VX_DCR_B200_RT_KERNEL, int(kernel))
 
     def close(self):
         for b in list(self.bufs.values()) + [self.out, self.args, self.krnl]:

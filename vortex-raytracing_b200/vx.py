@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libvortex-b200.so")
 VX_MEM_READ, VX_MEM_WRITE, VX_MEM_READ_WRITE = 1, 2, 3
 VX_MAX_TIMEOUT = 24 * 60 * 60 * 1000
 VX_DCR_BASE_RTX_TLAS_PTR, VX_DCR_BASE_RTX_BLAS_PTR, VX_DCR_BASE_RTX_BVH_PTR, VX_DCR_BASE_RTX_TRI_PTR = 6, 7, 8, 9
-VX_DCR_B200_RT_MODE, VX_DCR_B200_RT_LAYOUT, VX_DCR_B200_RT_ORDER, VX_DCR_B200_RT_CAMERA = 0x0F0, 0x0F1, 0x0F2, 0x0F3
+VX_DCR_B200_RT_MODE, VX_DCR_B200_RT_LAYOUT, VX_DCR_B200_RT_ORDER, VX_DCR_B200_RT_CAMERA, VX_DCR_B200_RT_KERNEL = 0x0F0, 0x0F1, 0x0F2, 0x0F3, 0x0F4
 MODE_SHADOW, MODE_DIFFUSE = 1, 2
 
 # every symbol include/vortex_b200.h declares (tests check that the library exports all of them)
