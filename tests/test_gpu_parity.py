@@ -22,8 +22,8 @@ def oracle():
     return best_oracle()
 
 
-def check_render(tr, sc, mode, strict, tol):
-    tr.set_mode(mode, strict)
+def check_render(tr, sc, mode, strict, tol, kernel=0):
+    tr.set_mode(mode, strict, kernel=kernel)
     img = tr.run()
     ref, _ = sc.render(mode=mode, threads=sc.o.hw_threads())
     d = channel_diff(img, ref)
@@ -76,9 +76,11 @@ def test_render_and_hits_vs_oracle(oracle, name, mk, w, h, depth, mode, kw):
     karg = sc.setup(w, h, max_depth=depth, **kw)
     tr = tracer_for(sc, karg)
     try:
-        img_s, ref = check_render(tr, sc, mode, 1, 0)
-        assert np.array_equal(img_s, ref)
-        check_render(tr, sc, mode, 0, 1)
+        for kernel in (0, 1):     # 0 = ray state machine (default), 1 = one pixel per lane
+            img_s, ref = check_render(tr, sc, mode, 1, 0, kernel)
+            assert np.array_equal(img_s, ref)
+            check_render(tr, sc, mode, 0, 1, kernel)
+        tr.set_mode(mode, 0, kernel=0)
         ref_hits = sc.trace_primary(threads=oracle.hw_threads())
         for strict in (1, 0):
             tr.set_mode(mode, strict)
@@ -207,3 +209,30 @@ def test_abi_error_behaviour():
         assert dev.ready_wait(10) is None                                   # nothing pending
     finally:
         dev.close()
+
+
+REF_APP = os.path.join(ROOT, "oracle", "_ref", "raycast")
+
+
+@pytest.mark.skipif(not (os.path.exists(REF_APP) and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "assets", "teapot.obj"))),
+                    reason="the compiled reference app (oracle/_ref/raycast + assets) did not travel with the snapshot")
+@pytest.mark.parametrize("flags,md5", [(["-w64", "-h64"], "a8248b0896d09d1b3b98b67f5c43ce6c"),
+                                       (["-n3", "-d4", "-w64", "-h64"], "d8ecb7285f1920568d8f32abe0ad600c")],
+                         ids=["teapot", "three_teapots_mirror_d4"])
+@pytest.mark.parametrize("order", ["1", "0"], ids=["strict", "fast"])
+def test_unmodified_reference_app_runs_on_b200(tmp_path, flags, md5, order):
+    """drop-in proof: the reference's own raycast binary (its Tracer, Scene, BVH, OBJ/PNG loaders, linked against the reference
+    stub libvortex.so) with VORTEX_DRIVER=b200 -> dlopen(libvortex-b200.so) -> vx_dev_init.  The PPM it writes must be
+    byte-identical to the one its own CPU path (-c) writes (md5 recorded in BASELINE.md 2)."""
+    import hashlib
+    import subprocess
+    lib_dir = os.path.dirname(vx.LIB_PATH)
+    kernel = tmp_path / "kernel.vxbin"
+    kernel.write_bytes(vx.DUMMY_KERNEL_IMAGE)
+    out = tmp_path / "out.ppm"
+    env = dict(os.environ, VORTEX_DRIVER="b200", VORTEX_B200_ORDER=order,
+               LD_LIBRARY_PATH=lib_dir + ":" + os.path.dirname(REF_APP) + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    r = subprocess.run([REF_APP, "-k", str(kernel), "-o", str(out)] + flags, cwd=os.path.dirname(REF_APP), env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout
+    assert hashlib.md5(out.read_bytes()).hexdigest() == md5, r.stdout[-400:]

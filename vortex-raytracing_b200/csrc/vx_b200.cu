@@ -88,6 +88,10 @@ public:
     part_.band_rows = 8;
     if (part_.world == 0) part_.world = 1;
     if (part_.rank >= part_.world) return fail("VORTEX_B200_RANK %u >= VORTEX_B200_WORLD %u", part_.rank, part_.world);
+    // defaults of the b200-private DCRs for hosts that cannot write them (an unmodified Vortex application)
+    if (getenv("VORTEX_B200_MODE")) dcrs_[VX_DCR_B200_RT_MODE] = (uint32_t)env_u64("VORTEX_B200_MODE", 0);
+    if (getenv("VORTEX_B200_ORDER")) dcrs_[VX_DCR_B200_RT_ORDER] = (uint32_t)env_u64("VORTEX_B200_ORDER", 0);
+    if (getenv("VORTEX_B200_KERNEL")) dcrs_[VX_DCR_B200_RT_KERNEL] = (uint32_t)env_u64("VORTEX_B200_KERNEL", 0);
     CUDA_TRY(cudaStreamSynchronize(stream_));
     return 0;
   }
