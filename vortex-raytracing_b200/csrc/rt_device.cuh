@@ -48,6 +48,25 @@ __device__ __forceinline__ float slab(float4 lo, float4 hi, f3 o, f3 id, bool na
   return tmin;
 }
 
+// Same test, split into (tmin, passed): the reference's "d != LARGE_FLOAT && d < hit.dist" (render.h:109-110) equals
+// "passed && tmin < hit.dist" because hit.dist never exceeds LARGE_FLOAT.
+__device__ __forceinline__ bool slab_hit(float4 lo, float4 hi, f3 o, f3 id, bool nan_safe, float limit, float &tmin_out) {
+  float tx1 = (lo.x - o.x) * id.x, tx2 = (hi.x - o.x) * id.x;
+  float ty1 = (lo.y - o.y) * id.y, ty2 = (hi.y - o.y) * id.y;
+  float tz1 = (lo.z - o.z) * id.z, tz2 = (hi.z - o.z) * id.z;
+  float tmin, tmax;
+  if (!nan_safe) {
+    tmin = fmaxf(fmaxf(fminf(tx1, tx2), fminf(ty1, ty2)), fminf(tz1, tz2));
+    tmax = fminf(fminf(fmaxf(tx1, tx2), fmaxf(ty1, ty2)), fmaxf(tz1, tz2));
+  } else {
+    tmin = std_min(tx1, tx2), tmax = std_max(tx1, tx2);
+    tmin = std_max(tmin, std_min(ty1, ty2)), tmax = std_min(tmax, std_max(ty1, ty2));
+    tmin = std_max(tmin, std_min(tz1, tz2)), tmax = std_min(tmax, std_max(tz1, tz2));
+  }
+  tmin_out = tmin;
+  return !(tmax < tmin || tmax <= 0) && (tmin < limit);
+}
+
 // ---- ray_t::intersect(tri) (geometry.h:1416-1445), triangle in edge form ----
 __device__ __forceinline__ bool moller_trumbore(const Ray &r, f3 v0, f3 e1, f3 e2, float &t, float &w1o, float &w2o) {
   f3 h = cross3(r.d, e2);

@@ -28,9 +28,13 @@ constexpr uint32_t kReadNode = 15u;
 constexpr uint32_t S_EMPTY = 0, S_TRAV = 1, S_DONE = 2, S_MASK = 3;
 constexpr uint32_t F_ANY = 4, F_NAN = 8, F_INBLAS = 16, F_OCCL = 32;
 
-constexpr uint32_t kRefillQuorum = 20;   // run GEN/POST when fewer lanes than this are traversing
-constexpr uint32_t kInnerQuorum = 8;     // leave the inner-node loop when fewer lanes than this have an inner node
-constexpr uint32_t kChunk = 256;         // pixels a warp reserves per atomic
+// Scheduling parameters come with the launch (RenderA::quorum_refill / quorum_inner / chunk; defaults 12 / 8 / 32 chosen by
+// the sweep in profiles/r01_sweep_quorum_chunk.txt): GEN/POST run when fewer than quorum_refill lanes are traversing, the
+// inner-node loop is left when fewer than quorum_inner lanes hold an inner node, a warp reserves `chunk` pixels (one 8x4
+// tile) per atomicAdd — 256-pixel chunks left SMs idle 32-39 % of the kernel (ncu sm__cycles_active avg vs elapsed).
+#ifndef VXB_MIN_BLOCKS
+#define VXB_MIN_BLOCKS 4
+#endif
 
 // shared-memory columns (one 32-bit word per thread each)
 enum : uint32_t {
@@ -46,12 +50,15 @@ struct Lane {
   float dist, bx, by;   // closest hit so far
   uint32_t hblas, htri;
   uint32_t cur, sp, st;
-  uint32_t node_base, blas;
+  uint32_t blas;
+  const uint8_t *nodes;   // first node of the instance being traversed
 };
 
+// cursor of a child node: small leaves and inner nodes carry (triCount, leftFirst) so the node is never re-read; payloads
+// fit 27 bits because the launch refuses scenes with >= 2^27 nodes or triangle slots (kMachineMaxNodes)
 __device__ __forceinline__ uint32_t enc_child(uint32_t leftFirst, uint32_t triCount, uint32_t nodeIdx) {
-  if (triCount < kReadNode && leftFirst <= kPay) return (triCount << kKindShift) | leftFirst;
-  return (kReadNode << kKindShift) | nodeIdx;
+  bool direct = triCount < kReadNode;
+  return ((direct ? triCount : kReadNode) << kKindShift) | (direct ? leftFirst : nodeIdx);
 }
 
 __device__ __forceinline__ void set_recip(Lane &L) {
@@ -99,14 +106,13 @@ __device__ __forceinline__ void pop(Lane &L, const uint32_t *stk_e, const float 
 // one inner-node visit inside an instance: both children are one 64-byte record (render.h:100-124)
 template <bool STRICT, bool STATS>
 __device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool careful, uint32_t *stk_e, float *stk_d, Local &lc) {
-  uint32_t first = L.cur & kPay;
-  const uint8_t *pair = sc.nodes + ((size_t)L.node_base + first) * sizeof(BvhNodeA);
+  uint32_t first = L.cur;   // kind bits are zero for an inner pair
+  const uint8_t *pair = L.nodes + (size_t)first * sizeof(BvhNodeA);
   float4 l0 = ldg4(pair), l1 = ldg4(pair + 16), r0 = ldg4(pair + 32), r1 = ldg4(pair + 48);
-  float dL = slab(l0, l1, L.o, L.id, careful);
-  float dR = slab(r0, r1, L.o, L.id, careful);
+  float dL, dR;
+  bool hitL = slab_hit(l0, l1, L.o, L.id, careful, L.dist, dL);
+  bool hitR = slab_hit(r0, r1, L.o, L.id, careful, L.dist, dR);
   if (STATS) lc.box += 2;
-  bool hitL = (dL != kLargeFloat) && (dL < L.dist);
-  bool hitR = (dR != kLargeFloat) && (dR < L.dist);
   uint32_t eL = enc_child(__float_as_uint(l0.w), __float_as_uint(l1.w), first);
   uint32_t eR = enc_child(__float_as_uint(r0.w), __float_as_uint(r1.w), first + 1);
   if (hitL && hitR) {
@@ -147,7 +153,7 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       L.d = od, L.o = oo;
       L.st |= F_INBLAS;
       set_recip(L);
-      L.node_base = __ldg(&blas->bvh_offset);
+      L.nodes = sc.nodes + (size_t)__ldg(&blas->bvh_offset) * sizeof(BvhNodeA);
       L.blas = bi;
       L.cur = kReadNode << kKindShift;   // node 0 of the instance
       if (STATS) lc.blas++;
@@ -156,11 +162,10 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       const uint8_t *pl = reinterpret_cast<const uint8_t *>(sc.tlas + left);
       const uint8_t *pr = reinterpret_cast<const uint8_t *>(sc.tlas + right);
       bool careful = (L.st & F_NAN) != 0;
-      float dL = slab(ldg4(pl), ldg4(pl + 16), L.o, L.id, careful);
-      float dR = slab(ldg4(pr), ldg4(pr + 16), L.o, L.id, careful);
+      float dL, dR;
+      bool hitL = slab_hit(ldg4(pl), ldg4(pl + 16), L.o, L.id, careful, L.dist, dL);
+      bool hitR = slab_hit(ldg4(pr), ldg4(pr + 16), L.o, L.id, careful, L.dist, dR);
       if (STATS) lc.box += 2;
-      bool hitL = (dL != kLargeFloat) && (dL < L.dist);
-      bool hitR = (dR != kLargeFloat) && (dR < L.dist);
       if (hitL && hitR) {   // near child first at this level (render.h:175-180)
         bool swap = dL > dR;
         stk_e[L.sp] = kTlasTag | (swap ? left : right);
@@ -179,8 +184,17 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
   }
   uint32_t kind = (L.cur >> kKindShift) & 15u, first = L.cur & kPay, count = kind;
   if (kind == kReadNode) {
-    const uint8_t *n = sc.nodes + ((size_t)L.node_base + first) * sizeof(BvhNodeA);
+    const uint8_t *n = L.nodes + (size_t)first * sizeof(BvhNodeA);
     float4 a = ldg4(n), b = ldg4(n + 16);
+    if (!STRICT && first == 0) {
+      // instance root: the reference never tests this box, but every box below it lies inside it and IEEE rounding is
+      // monotonic, so a ray that fails here fails both children too — rejecting it now skips only failing tests
+      float t0;
+      if (!slab_hit(a, b, L.o, L.id, (L.st & F_NAN) != 0, L.dist, t0)) {
+        pop<STRICT>(L, stk_e, stk_d);
+        return;
+      }
+    }
     first = __float_as_uint(a.w);
     count = __float_as_uint(b.w);
     if (count == 0) {   // an inner node after all: its child pair is visited by the inner loop
@@ -216,11 +230,12 @@ template <bool STRICT, bool STATS>
 __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &sc, uint32_t quorum, uint32_t inner_quorum, uint32_t *stk_e,
                                          float *stk_d, Local &lc) {
   for (;;) {
+    // warp-uniform choice of the NaN-exact min/max path (no divergence); F_NAN only changes in step_other / start_ray
+    const bool careful = __any_sync(0xffffffffu, (L.st & (S_MASK | F_NAN)) == (S_TRAV | F_NAN));
     for (;;) {
       bool inner = is_inner(L);
       unsigned m = __ballot_sync(0xffffffffu, inner);
       if ((uint32_t)__popc(m) < inner_quorum) break;
-      bool careful = __any_sync(0xffffffffu, inner && (L.st & F_NAN));   // warp-uniform: no divergence on the NaN-exact min/max path
       if (inner) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);
     }
     if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
@@ -353,7 +368,7 @@ __device__ __forceinline__ void post(Lane &L, const Smem &sm, const RenderA &p, 
 }
 
 template <uint32_t MODE, bool STRICT, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads) k_render_m(const __grid_constant__ RenderA p) {
+__global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(const __grid_constant__ RenderA p) {
   constexpr uint32_t kCols = (MODE & 1u) ? C_SHADOW_END : C_BASE_END;
   __shared__ float s_cols[kCols * kBlockThreads];
   uint32_t stk_e[kStackSize];
@@ -371,7 +386,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_render_m(const __grid_constan
   f.total = nbands * f.tiles_per_band * 32u;
 
   Lane L;
-  L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.node_base = 0, L.blas = 0;
+  L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.blas = 0;
   L.o = L.d = L.id = mk3(0, 0, 0);
   Local lc{0, 0, 0, 0, 0};
   uint32_t chunk_next = 0, chunk_end = 0;
@@ -380,9 +395,9 @@ __global__ void __launch_bounds__(kBlockThreads) k_render_m(const __grid_constan
   for (;;) {
     unsigned trav = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
     unsigned done = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_DONE);
-    const uint32_t quorum = exhausted ? 1u : kRefillQuorum;
+    const uint32_t quorum = exhausted ? 1u : p.quorum_refill;
     if (trav && ((uint32_t)__popc(trav) >= quorum || (!done && exhausted))) {
-      traverse<STRICT, STATS>(L, sm, p.scene, quorum, exhausted ? 1u : kInnerQuorum, stk_e, stk_d, lc);
+      traverse<STRICT, STATS>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk_e, stk_d, lc);
       continue;
     }
     if (done) {
@@ -398,14 +413,14 @@ __global__ void __launch_bounds__(kBlockThreads) k_render_m(const __grid_constan
     while (need) {
       if (chunk_next == chunk_end) {
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(p.tile_counter, kChunk);
+        if (lane == 0) base = atomicAdd(p.tile_counter, p.chunk);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= f.total) {
           exhausted = true;
           break;
         }
         chunk_next = base;
-        chunk_end = min(base + kChunk, f.total);
+        chunk_end = min(base + p.chunk, f.total);
       }
       uint32_t avail = chunk_end - chunk_next;
       bool mine = (need >> lane) & 1u;

@@ -34,6 +34,9 @@ struct RenderA {
   WorkCounters *counters;
   uint32_t *tile_counter;   // device word, zeroed before each launch
   int stats;                // gather box/tri/blas counters
+  uint32_t quorum_refill;   // ray state machine: run GEN/POST when fewer lanes than this are traversing
+  uint32_t chunk;           //                    pixels a warp reserves per atomicAdd on the work counter
+  uint32_t quorum_inner;    //                    leave the inner-node loop when fewer lanes than this hold an inner node
 };
 
 struct TraceA {
