@@ -30,7 +30,7 @@ typedef struct {
   const uint8_t *mem; uint64_t base, size;
   uint32_t tlas, blas, qbvh, tri;           /* DCRs 0x006..0x009 (rt_traversal.cpp:35-38) */
 } rtu_image;
-typedef struct { uint64_t calls, nodes, blas, tris, restarts; } rtu_work;
+typedef struct { uint64_t calls, nodes, blas, tris, restarts, wraps; } rtu_work;
 
 #pragma pack(push, 1)
 typedef struct { uint8_t meta; uint8_t q[6]; } rtu_child;
@@ -167,6 +167,7 @@ static int traverse(const rtu_image *im, const rtu_ray *ray, rtu_hit *hit, float
       /* k == WIDTH: keep only the farthest.  With n == 0 the reference's "size()-1" wraps and its loop spins over an
          empty vector (a no-op); the outcome is the same as dropping nothing. */
       uint32_t drop = (k == RTU_WIDTH) ? (n > 0 ? (uint32_t)n - 1 : 0) : k;
+      if (w && k == RTU_WIDTH && n == 0) w->wraps++;   /* where the compiled reference spins for 2^32 iterations */
       while (drop-- > 0 && n > 0) n--;                                                   /* pop_back = drop the nearest */
       if (n == 0) {
         done = trav_pop(im, &base_ptr, &node_ptr, &level, trail, stack, w);
@@ -336,7 +337,7 @@ static v3 shade(const rtu_image *im, const rtu_karg *a, const rtu_ray *ray, uint
 /* ================================================================ C API (same shapes as oracle/ref_harness) ======== */
 typedef struct {
   rtu_image im; const rtu_karg *arg; uint32_t camera; uint32_t *out;
-  const float *rays; uint64_t n; rtu_hit *hits;
+  const float *rays; uint64_t n; rtu_hit *hits; uint8_t *flags;
   uint32_t next; pthread_mutex_t mu; rtu_work work; uint64_t shaded, total_rays; int count;
 } rtu_job;
 
@@ -351,11 +352,14 @@ static void *trace_worker(void *p) {
     uint64_t e = b + 1024 < j->n ? b + 1024 : j->n;
     for (uint64_t i = b; i < e; ++i) {
       rtu_ray r = {j->rays[6 * i], j->rays[6 * i + 1], j->rays[6 * i + 2], j->rays[6 * i + 3], j->rays[6 * i + 4], j->rays[6 * i + 5]};
-      trace_one(&j->im, &r, &j->hits[i], j->count ? &w : NULL);
+      uint64_t wraps0 = w.wraps;
+      trace_one(&j->im, &r, &j->hits[i], (j->count || j->flags) ? &w : NULL);
+      if (j->flags) j->flags[i] = (uint8_t)(w.wraps != wraps0);
     }
   }
   pthread_mutex_lock(&j->mu);
   j->work.calls += w.calls, j->work.nodes += w.nodes, j->work.blas += w.blas, j->work.tris += w.tris, j->work.restarts += w.restarts;
+  j->work.wraps += w.wraps;
   pthread_mutex_unlock(&j->mu);
   return NULL;
 }
@@ -395,14 +399,16 @@ static void run_job(rtu_job *j, void *(*fn)(void *), uint32_t threads) {
   pthread_mutex_destroy(&j->mu);
 }
 
-/* work (optional, 6 x u64): traverse calls, nodes read, BLAS entered, triangles tested, restarts, shaded hits */
+/* work (optional, 6 x u64): traverse calls, nodes read, BLAS entered, triangles tested, restarts, shaded hits (render) or
+   size()-1 wrap events (trace_rays) */
 void port_rtu_trace_rays(const uint8_t *mem, uint64_t base, uint64_t size, uint32_t tlas, uint32_t blas, uint32_t qbvh, uint32_t tri,
-                         const float *rays, uint64_t n, void *hits, uint32_t threads, uint64_t *work) {
+                         const float *rays, uint64_t n, void *hits, uint32_t threads, uint64_t *work, uint8_t *wrap_flags) {
   rtu_job j; memset(&j, 0, sizeof(j));
+  j.flags = wrap_flags;   /* optional, one byte per ray: 1 = this ray reaches the reference's size()-1 wrap (rt_traversal.cpp:81) */
   j.im.mem = mem, j.im.base = base, j.im.size = size, j.im.tlas = tlas, j.im.blas = blas, j.im.qbvh = qbvh, j.im.tri = tri;
   j.rays = rays, j.n = n, j.hits = (rtu_hit *)hits, j.count = work != NULL;
   run_job(&j, trace_worker, threads);
-  if (work) work[0] = j.work.calls, work[1] = j.work.nodes, work[2] = j.work.blas, work[3] = j.work.tris, work[4] = j.work.restarts, work[5] = 0;
+  if (work) work[0] = j.work.calls, work[1] = j.work.nodes, work[2] = j.work.blas, work[3] = j.work.tris, work[4] = j.work.restarts, work[5] = j.work.wraps;
 }
 
 void port_rtuh_render(const uint8_t *mem, uint64_t base, uint64_t size, const void *karg, const uint32_t *dcr, uint32_t camera,

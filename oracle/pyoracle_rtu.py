@@ -215,20 +215,30 @@ class RtuPort:
             raise FileNotFoundError(f"{PORT_SO} missing: run `make -C oracle port`")
         L = self.lib = C.CDLL(PORT_SO)
         L.port_rtu_trace_rays.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
-                                          C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p]
+                                          C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.port_rtuh_render.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                        C.c_uint32, C.c_void_p]
         L.port_rtuh_primary_rays.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
 
-    def trace_rays(self, img, rays, threads=1, want_work=False):
+    def trace_rays(self, img, rays, threads=1, want_work=False, want_wrap_flags=False):
+        """want_wrap_flags: also return one byte per ray, 1 where traversal reaches the reference's `size()-1` wrap
+        (rt_traversal.cpp:81 with k == 4 and no surviving child) — the compiled reference spins 2^32 iterations there."""
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
         hits = np.zeros(rays.shape[0], dtype=HIT_DT)
         work = np.zeros(6, dtype=np.uint64)
+        flags = np.zeros(rays.shape[0], dtype=np.uint8) if want_wrap_flags else None
         d = img.dcr
         self.lib.port_rtu_trace_rays(img.mem.ctypes.data, img.base, len(img.mem), int(d[0]), int(d[1]), int(d[2]), int(d[3]),
                                      rays.ctypes.data, rays.shape[0], hits.ctypes.data, threads,
-                                     work.ctypes.data if want_work else None)
-        return (hits, dict(zip(WORK_NAMES, (int(x) for x in work)))) if want_work else hits
+                                     work.ctypes.data if want_work else None, flags.ctypes.data if want_wrap_flags else None)
+        out = (hits,)
+        if want_work:
+            w = dict(zip(WORK_NAMES, (int(x) for x in work)))
+            w["wraps"] = w.pop("shaded_hits")
+            out += (w,)
+        if want_wrap_flags:
+            out += (flags,)
+        return out if len(out) > 1 else hits
 
     def primary_rays(self, img, camera):
         w, h = int(img.karg["dst_width"][0]), int(img.karg["dst_height"][0])

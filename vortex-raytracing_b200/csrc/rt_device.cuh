@@ -22,7 +22,7 @@ struct Hit {
   uint32_t blas, tri;
 };
 struct Local {   // per-thread work counters
-  uint32_t rays, box, tri, blas, shaded;
+  uint32_t rays, box, tri, blas, shaded, err;
 };
 
 __device__ __forceinline__ float4 ldg4(const void *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
@@ -136,6 +136,7 @@ __device__ __forceinline__ Surface surface_at(const SceneA &sc, const Ray &ray, 
 
 __device__ __forceinline__ void flush_counters(WorkCounters *c, const Local &lc, bool stats) {
   unsigned rays = __reduce_add_sync(0xffffffffu, lc.rays);
+  unsigned err = __reduce_or_sync(0xffffffffu, lc.err);
   unsigned box = 0, tri = 0, blas = 0, shaded = 0;
   if (stats) {
     box = __reduce_add_sync(0xffffffffu, lc.box);
@@ -145,6 +146,7 @@ __device__ __forceinline__ void flush_counters(WorkCounters *c, const Local &lc,
   }
   if ((threadIdx.x & 31) == 0) {
     atomicAdd(&c->rays, (unsigned long long)rays);
+    if (err) atomicOr(&c->errors, (unsigned long long)err);
     if (stats) {
       atomicAdd(&c->box_tests, (unsigned long long)box);
       atomicAdd(&c->tri_tests, (unsigned long long)tri);

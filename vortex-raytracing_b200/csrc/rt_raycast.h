@@ -22,6 +22,7 @@ struct Partition {
 
 struct WorkCounters {       // device-resident, zeroed before each run
   unsigned long long rays, box_tests, tri_tests, blas_entered, shaded_hits;
+  unsigned long long errors;   // bit 0: a traversal stack overflowed (the run is reported as failed)
 };
 
 struct RenderA {

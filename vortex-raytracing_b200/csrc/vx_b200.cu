@@ -101,7 +101,8 @@ public:
     cudaSetDevice(cuda_dev_);
     if (stream_) cudaStreamSynchronize(stream_);
     if (gtri_) cudaFree(gtri_);
-    if (rtu_) rtu_release(rtu_);
+    if (rtu_nodes_) cudaFree(rtu_nodes_);
+    if (rtu_tri_) cudaFree(rtu_tri_);
     if (counters_) cudaFree(counters_);
     if (tile_counter_) cudaFree(tile_counter_);
     if (h_counters_) cudaFreeHost(h_counters_);
@@ -110,7 +111,7 @@ public:
     if (ev_prep_) cudaEventDestroy(ev_prep_);
     if (ev_end_) cudaEventDestroy(ev_end_);
     if (stream_) cudaStreamDestroy(stream_);
-    gtri_ = nullptr, rtu_ = nullptr, counters_ = nullptr, tile_counter_ = nullptr, h_counters_ = nullptr, arena_ = nullptr;
+    gtri_ = nullptr, rtu_nodes_ = nullptr, rtu_tri_ = nullptr, counters_ = nullptr, tile_counter_ = nullptr, h_counters_ = nullptr, arena_ = nullptr;
     stream_ = nullptr;
     cuda_dev_ = -1;
   }
@@ -366,6 +367,7 @@ private:
     stats_.tri_tests = h_counters_->tri_tests;
     stats_.blas_entered = h_counters_->blas_entered;
     stats_.shaded_hits = h_counters_->shaded_hits;
+    if (h_counters_->errors) return fail("run failed on the device: traversal stack overflow (error bits 0x%llx)", (unsigned long long)h_counters_->errors);
     stats_.kernel_launches = launches_;
     stats_.prep_launches = prep_launches_;
     stats_.prep_ms = ms_prep;
@@ -447,6 +449,8 @@ private:
     return end_run_locked();
   }
 
+  // layout B: resolve the scene, (re)build the decoded-node / edge-form-triangle arrays if the uploads changed.
+  // Must run between begin_run_locked() and the ev_prep_ record (prep launches are timed separately).
   int rtu_scene_locked(const KernelArgB &a, RtuScene *sc) {
     // the RT unit reads its four scene pointers from DCRs 0x006..0x009 (sim/simx/rt_traversal.cpp:35-38);
     // hosts that never wrote them fall back to the kernel_arg_t fields
@@ -454,15 +458,48 @@ private:
     uint64_t blas_addr = dcrs_.count(VX_DCR_BASE_RTX_BLAS_PTR) ? dcr_get(VX_DCR_BASE_RTX_BLAS_PTR) : a.blas_addr;
     uint64_t qbvh_addr = dcrs_.count(VX_DCR_BASE_RTX_BVH_PTR) ? dcr_get(VX_DCR_BASE_RTX_BVH_PTR) : a.qBvh_addr;
     uint64_t tri_addr = dcrs_.count(VX_DCR_BASE_RTX_TRI_PTR) ? dcr_get(VX_DCR_BASE_RTX_TRI_PTR) : a.tri_addr;
-    if (resolve(tlas_addr, sizeof(QNodeB), 4, "tlas(q)", &sc->tlas)) return -1;
-    if (resolve(blas_addr, sizeof(BlasNodeB), 4, "blas", &sc->blas)) return -1;
-    if (resolve(qbvh_addr, sizeof(QNodeB), 4, "qBvh", &sc->qbvh)) return -1;
-    if (resolve(tri_addr, sizeof(TriA), 4, "tri", &sc->tri)) return -1;
-    if (resolve(a.triEx_addr, sizeof(TriExB), 4, "triEx", &sc->triEx)) return -1;
+    const QNodeB *tlas = nullptr, *qbvh = nullptr;
+    const TriA *tri = nullptr;
+    uint64_t tlas_bytes = 0, qbvh_bytes = 0, tri_bytes = 0, blas_bytes = 0, ex_bytes = 0, mat_bytes = 0, tex_bytes = 0;
+    uint64_t gen[3] = {0, 0, 0};
+    if (resolve(tlas_addr, sizeof(QNodeB), 4, "tlas(q)", &tlas, &tlas_bytes, &gen[0])) return -1;
+    if (resolve(blas_addr, sizeof(BlasNodeB), 4, "blas", &sc->blas, &blas_bytes)) return -1;
+    if (resolve(qbvh_addr, sizeof(QNodeB), 4, "qBvh", &qbvh, &qbvh_bytes, &gen[1])) return -1;
+    if (resolve(tri_addr, sizeof(TriA), 4, "tri", &tri, &tri_bytes, &gen[2])) return -1;
+    if (resolve(a.triEx_addr, sizeof(TriExB), 4, "triEx", &sc->triEx, &ex_bytes)) return -1;
     sc->mat = nullptr, sc->tex = nullptr;
-    if (a.mat_addr) { if (resolve(a.mat_addr, 4, 4, "mat", &sc->mat)) return -1; }
-    if (a.tex_addr) { if (resolve(a.tex_addr, 4, 4, "tex", &sc->tex)) return -1; }
-    sc->tlas_root = a.tlas_root;
+    if (a.mat_addr && space_.find(a.mat_addr, 1, nullptr)) { if (resolve(a.mat_addr, 4, 4, "mat", &sc->mat, &mat_bytes)) return -1; }
+    if (a.tex_addr && space_.find(a.tex_addr, 1, nullptr)) { if (resolve(a.tex_addr, 4, 4, "tex", &sc->tex, &tex_bytes)) return -1; }
+    uint64_t n_tlas = tlas_bytes / sizeof(QNodeB), n_bvh = qbvh_bytes / sizeof(QNodeB), n_tri = tri_bytes / sizeof(TriA);
+    if (n_tlas >= (1ull << 30) || n_bvh >= (1ull << 30) || n_tri > 0xFFFFFFFFull) return fail("layout B scene too large");
+    if (ex_bytes / sizeof(TriExB) < n_tri) n_tri = ex_bytes / sizeof(TriExB);   // shading indexes triEx by triIdx
+    uint64_t key[9] = {tlas_addr, qbvh_addr, tri_addr, gen[0], gen[1], gen[2], n_tlas, n_bvh, n_tri};
+    if (!rtu_valid_ || memcmp(key, rtu_key_, sizeof(key)) != 0) {
+      uint64_t need_nodes = n_tlas + n_bvh;
+      if (rtu_nodes_cap_ < need_nodes) {
+        if (rtu_nodes_) cudaFree(rtu_nodes_);
+        rtu_nodes_ = nullptr, rtu_nodes_cap_ = 0;
+        CUDA_TRY(cudaMalloc(&rtu_nodes_, need_nodes * sizeof(GpuNodeB)));
+        rtu_nodes_cap_ = need_nodes;
+      }
+      if (rtu_tri_cap_ < n_tri) {
+        if (rtu_tri_) cudaFree(rtu_tri_);
+        rtu_tri_ = nullptr, rtu_tri_cap_ = 0;
+        CUDA_TRY(cudaMalloc(&rtu_tri_, n_tri * sizeof(GpuTri)));
+        rtu_tri_cap_ = n_tri;
+      }
+      CUDA_TRY(launch_rtu_decode_nodes(tlas, rtu_nodes_, n_tlas, stream_));
+      CUDA_TRY(launch_rtu_decode_nodes(qbvh, rtu_nodes_ + n_tlas, n_bvh, stream_));
+      CUDA_TRY(launch_rtu_gather_tris(tri, rtu_tri_, n_tri, stream_));
+      launches_ += 3, prep_launches_ += 3;
+      memcpy(rtu_key_, key, sizeof(key));
+      rtu_valid_ = true;
+    }
+    sc->gtlas = rtu_nodes_, sc->gbvh = rtu_nodes_ + n_tlas, sc->gtri = rtu_tri_;
+    sc->n_tlas = (uint32_t)n_tlas, sc->n_bvh = (uint32_t)n_bvh, sc->n_tri = (uint32_t)n_tri;
+    sc->n_blas = (uint32_t)(blas_bytes / sizeof(BlasNodeB));
+    sc->n_mat = (uint32_t)(mat_bytes / sizeof(MaterialB)), sc->_pad = 0;
+    sc->tex_bytes = tex_bytes;
     return 0;
   }
 
@@ -472,12 +509,12 @@ private:
     memcpy(&a, args.data(), sizeof(a));
     if (a.dst_width == 0 || a.dst_height == 0) return fail("empty framebuffer");
     RtuRender p{};
-    if (rtu_scene_locked(a, &p.scene)) return -1;
     if (resolve(a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, 4, "framebuffer", &p.out)) return -1;
     if (begin_run_locked() != 0) return -1;
+    if (rtu_scene_locked(a, &p.scene)) return -1;
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.part = part_, p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
-    p.camera = dcr_get(VX_DCR_B200_RT_CAMERA);
+    p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
     int rc = launch_rtu_render(p, prop_.multiProcessorCount, stream_);
     if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
     launches_ += rc;
@@ -489,15 +526,15 @@ private:
     KernelArgB a;
     memcpy(&a, args.data(), sizeof(a));
     RtuTrace p{};
-    if (rtu_scene_locked(a, &p.scene)) return -1;
     uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
     if (resolve(hits_addr, n * sizeof(HitA), 4, "hits", &p.hits)) return -1;
     p.rays = nullptr;
     if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &p.rays)) return -1;
     if (begin_run_locked() != 0) return -1;
+    if (rtu_scene_locked(a, &p.scene)) return -1;
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.count = n, p.counters = counters_, p.stats = stats_on_;
-    p.camera = dcr_get(VX_DCR_B200_RT_CAMERA);
+    p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
     int rc = launch_rtu_trace(p, prop_.multiProcessorCount, stream_);
     if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
     launches_ += rc;
@@ -518,7 +555,11 @@ private:
   GpuTri *gtri_ = nullptr;
   uint64_t gtri_cap_ = 0, gtri_slots_ = 0;
   uint64_t gtri_key_[4] = {0, 0, 0, 0};
-  void *rtu_ = nullptr;
+  // layout-B decoded nodes (TLAS then BLAS) and edge-form triangles
+  GpuNodeB *rtu_nodes_ = nullptr;
+  GpuTri *rtu_tri_ = nullptr;
+  uint64_t rtu_nodes_cap_ = 0, rtu_tri_cap_ = 0, rtu_key_[9] = {0};
+  bool rtu_valid_ = false;
   // run bookkeeping
   WorkCounters *counters_ = nullptr, *h_counters_ = nullptr;
   uint32_t *tile_counter_ = nullptr;

@@ -228,3 +228,9 @@ class Device:
 # a minimal stand-in for kernel.vxbin: {min_vma, max_vma} header + 1 byte (runtime/stub/utils.cpp:25-61).
 # The b200 backend reserves the range like any driver and never executes the image.
 DUMMY_KERNEL_IMAGE = np.array([0x80000000, 0x80001000], dtype=np.uint64).tobytes() + b"\x00" * 16
+
+
+def dummy_image(vma):
+    """stand-in for a shader image linked at `vma` (the raytracing test links miss/closest/anyhit at 0x8010/20/30_0000,
+    tests/regression/raytracing/Makefile:56-59)"""
+    return np.array([vma, vma + 0x1000], dtype=np.uint64).tobytes() + b"\x00" * 16
