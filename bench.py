@@ -298,6 +298,7 @@ def run_b200(args, wl, name):
         for other in ("primary_4k_1m", "cfg2_4k_diffuse4_1m"):
             if other != name:
                 extra[other] = quick_run(other, local, kernel=args.kernel)
+        extra["rtu_1080p_primary_100k"] = quick_run_rtu(local, with_cpu=not args.no_cpu)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -355,6 +356,70 @@ def quick_run(name, local, steps=5, kernel=0):
     tr.close()
     return {"mrays_per_s": rays / (float(np.mean(ms)) * 1e3), "kernel_ms": float(np.mean(ms)), "rays_per_step": rays,
             "note": "kernel time only, L2 not flushed (working set > L2 for the 1M-triangle scenes' framebuffer+scene)"}
+
+
+def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
+    """layout B (simx RT-unit path, quantized BVH4): kernel-only Mrays/s of k_rtu_render on the cfg1 geometry, its algorithmic
+    bytes (52 B per node read + 52 B per instance entered + 36 B per triangle tested + 156 B per shaded hit + 4 B per
+    pixel, counted in the reference's own visiting order) and the CPU-RTU baseline (the reference's rt_traversal.cpp when
+    oracle/_ref travelled, else the C port) on a bounded band of rows."""
+    host, rtx = pkg("host"), pkg("rtx_tracer")
+    scenes = pkg("scenes")
+    mesh = scenes.heightfield(n)
+    bmesh = {"tris": mesh["tris"], "triex": mesh["triex"], "texid": np.zeros(mesh["tris"].shape[0], np.uint32),
+             "materials": [{"tex": mesh["tex"]}], "reflectivity": 0.0}
+    t0 = time.perf_counter()
+    hs = host.RtxHostScene([bmesh])
+    # the slight scene rotation the raytracing host keeps commented out (tracer.cpp:199-203) and the raycast host applies
+    # (raycast/tracer.cpp:157-158): RotateX(-pi/4) * RotateY(pi/4), so that the camera looks down on the terrain as in cfg1
+    ax, ay = np.float32(-np.pi / 4), np.float32(np.pi / 4)
+    rx = np.array([[1, 0, 0, 0], [0, np.cos(ax), -np.sin(ax), 0], [0, np.sin(ax), np.cos(ax), 0], [0, 0, 0, 1]], dtype=np.float32)
+    ry = np.array([[np.cos(ay), 0, np.sin(ay), 0], [0, 1, 0, 0], [-np.sin(ay), 0, np.cos(ay), 0], [0, 0, 0, 1]], dtype=np.float32)
+    hs.apply_transform(rx @ ry)
+    karg = hs.setup(w, h, spp=1, max_depth=1)
+    bufs = hs.buffers()
+    build_s = time.perf_counter() - t0
+    tr = rtx.RtxTracer(w, h, 1, 1, cuda_device=local).init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names}, camera=rtx.CAMERA_PINHOLE)
+    tr._upload_args()
+    ms = []
+    for i in range(steps + 3):
+        tr.launch()
+        if i >= 3:
+            ms.append(tr.dev.last_kernel_ms())
+    rays = tr.dev.stats()["rays"]
+    tr.set_order(1)
+    tr.dev.enable_stats(True)
+    tr.launch()
+    wk = tr.dev.stats()
+    strict_ms = tr.dev.last_kernel_ms()
+    tr.close()
+    abytes = 52 * wk["box_tests"] + 52 * wk["blas_entered"] + 36 * wk["tri_tests"] + 156 * wk["shaded_hits"] + 4 * w * h
+    k_ms = float(np.mean(ms))
+    hbm, _, _ = peaks()
+    out = {"mrays_per_s": rays / (k_ms * 1e3), "kernel": "k_rtu_render (fast order)", "kernel_ms": k_ms, "rays_per_step": rays,
+           "strict_order_kernel_ms": strict_ms, "host_bvh4_build_s": round(build_s, 3),
+           "algorithmic_bytes_per_ray": abytes / max(1, rays), "roofline_hbm_frac": abytes / (k_ms * 1e-3) / 1e9 / hbm,
+           "work_per_ray": {"nodes": wk["box_tests"] / max(1, rays), "tri_tests": wk["tri_tests"] / max(1, rays),
+                            "blas_entered": wk["blas_entered"] / max(1, rays), "shaded_hits": wk["shaded_hits"] / max(1, rays)},
+           "note": "kernel time only, L2 not flushed; algorithmic work = the reference's trail/short-stack order (strict)"}
+    if with_cpu:
+        R = importlib.import_module("oracle.pyoracle_rtu")
+        orc = R.best()
+        img = R.Image(bufs, karg)
+        rows = 64
+        rays_cpu = orc.primary_rays(img, 1).reshape(h, w, 6)[(h - rows) // 2:(h - rows) // 2 + rows].reshape(-1, 6)
+        threads = os.cpu_count() or 1
+        best = None
+        for _ in range(2):
+            t0 = time.perf_counter()
+            orc.trace_rays(img, rays_cpu, threads=threads)
+            dt = time.perf_counter() - t0
+            best = dt if best is None or dt < best else best
+        out["cpu_rtu_baseline"] = {"value": len(rays_cpu) / best / 1e6, "unit": "Mrays/s", "cores": threads,
+                                   "kind": "reference" if orc.name == "ref" else "port",
+                                   "sample": f"traversal of the {rows} centre rows of {w}x{h} (sim/simx/rt_traversal.cpp order), best of 2"}
+    return out
 
 
 def main():

@@ -46,6 +46,41 @@ void vxh_setup(vxh_scene_h scene, void *kernel_arg_192, uint32_t width, uint32_t
                float camera_vfov_deg, float zoom, int rotate_scene, const float *light_pos, const float *light_color,
                const float *ambient, const float *background);
 
+
+/* ---- layout B: the RT-unit ("raytracing") host path -------------------------------------------------------------------
+ * Scene::init + BVH (BVH4 build + quantize) + TLAS (build + quantize) + Tracer::setup of the reference raytracing host
+ * (tests/regression/raytracing/scene.cpp:17-119, bvh.cpp:12-260,262-623, tracer.cpp:195-235), emitting its byte layouts
+ * (raytracing/common.h:20-99,164-195): triangles physically in leaf order, 52-byte quantized BVH4 nodes, quantized TLAS
+ * (node 0 = root), blas_node_t, material_info_t, kernel_arg_t (216 B).  Deterministic (the reference builder is not),
+ * conservative quantization verified against the RT unit's decode (sim/simx/rt_traversal.cpp:61-67). */
+typedef void *vxh_rtx_scene_h;
+
+typedef struct {
+  const void *tri;    uint64_t tri_bytes;     /* tri_t[] 36 B, reordered into leaf order */
+  const void *triEx;  uint64_t triEx_bytes;   /* tri_ex_t[] 64 B (texId = global material index), same order */
+  const void *triIdx; uint64_t triIdx_bytes;  /* uint32_t[] identity (unused by the RT unit) */
+  const void *mat;    uint64_t mat_bytes;     /* material_info_t[] 88 B */
+  const void *tex;    uint64_t tex_bytes;
+  const void *bvh;    uint64_t bvh_bytes;     /* unquantized helper tree (uploaded by the reference host, unused by the RT unit) */
+  const void *qbvh;   uint64_t qbvh_bytes;    /* bvh_quantized_node_t[] 52 B, 2*N allocated */
+  const void *blas;   uint64_t blas_bytes;    /* blas_node_t[] 160 B */
+  const void *tlas;   uint64_t tlas_bytes;    /* QUANTIZED TLAS nodes, 52 B */
+  uint32_t tlas_root, bvh_nodes_used, tlas_nodes_used, _pad;
+} vxh_rtx_scene_view_t;
+
+/* triex16: 16 words per triangle (15 floats N0 N1 N2 uv0 uv1 uv2 + uint32 texId local to its mesh); mats: n_mats[i]
+ * material_info_t records per mesh (tex_offset = byte offset into `tex`); reflectivity/transforms: per mesh or NULL. */
+vxh_rtx_scene_h vxh_rtx_scene_create(uint32_t n_meshes, const uint32_t *tri_counts, const float *tris, const uint32_t *triex16,
+                                     const uint32_t *n_mats, const void *mats, const uint8_t *tex, uint64_t tex_bytes,
+                                     const float *reflectivity, const float *transforms, int threads);
+void vxh_rtx_scene_apply_transform(vxh_rtx_scene_h scene, const float *m16);
+void vxh_rtx_scene_build(vxh_rtx_scene_h scene);
+void vxh_rtx_scene_view(vxh_rtx_scene_h scene, vxh_rtx_scene_view_t *view);
+void vxh_rtx_scene_free(vxh_rtx_scene_h scene);
+void vxh_rtx_setup(vxh_rtx_scene_h scene, void *kernel_arg_216, uint32_t width, uint32_t height, uint32_t spp, uint32_t max_depth,
+                   float camera_vfov_deg, float zoom, const float *light_pos, const float *light_color, const float *ambient,
+                   const float *background);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,7 +14,7 @@ from rt_common import ROOT, assert_hit_gates, best_oracle, channel_diff, hit_par
 
 pytestmark = pytest.mark.gpu
 po = pyoracle()
-GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")))
+GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "ref_*.npz")))
 
 
 @pytest.fixture(scope="module")

@@ -83,3 +83,38 @@ def test_rtu_scene_vs_oracle(name):
 def test_rtu_golden(path):
     g, karg = load_golden(path)
     check_scene(g, karg, int(g["camera"]), g["hits"].view(R.HIT_DT), g["image"])
+
+
+def test_rtu_product_builder_vs_oracle():
+    """scene prepared by the product's own layout-B host builder (vxh_rtx_*), ~100K triangles"""
+    import importlib
+    from rt_common import scenes
+    from rtu_common import b_mesh
+    host = importlib.import_module("vortex-raytracing_b200.host")
+    hs = host.RtxHostScene([b_mesh(scenes.heightfield(224), two_materials=True)])
+    karg = hs.setup(480, 270)
+    check_scene(hs.buffers(), karg, 1)
+
+
+def test_rtu_full_size_fast_equals_strict():
+    """BASELINE configs[1] geometry at 1920x1080 in layout B: the fast order returns the hit records of the reference's
+    own visiting order (strict) — a size-independent check that needs no CPU run"""
+    import importlib
+    from rt_common import scenes
+    from rtu_common import b_mesh
+    host = importlib.import_module("vortex-raytracing_b200.host")
+    hs = host.RtxHostScene([b_mesh(scenes.heightfield(224))])
+    karg = hs.setup(1920, 1080)
+    tr = tracer_b(hs.buffers(), karg, 1)
+    try:
+        tr.set_order(1)
+        hs_, fs = tr.trace_primary(), tr.run()
+        tr.set_order(0)
+        hf, ff = tr.trace_primary(), tr.run()
+        hp = hit_parity(hf, hs_)
+        assert_hit_gates(hp, False)
+        assert np.array_equal(hf["dist"], hs_["dist"])
+        assert channel_diff(ff, fs) <= 1
+        assert (hf["dist"] < 1e30).mean() > 0.2
+    finally:
+        tr.close()

@@ -13,7 +13,7 @@ import pytest
 from rt_common import ROOT, pyoracle, scenes
 
 po = pyoracle()
-GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")))
+GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "ref_*.npz")))
 
 
 @pytest.fixture(scope="module")

@@ -103,3 +103,117 @@ class HostScene:
         out["tlas_root"] = int(v.tlas_root)
         out["bvh_nodes_used"] = int(v.bvh_nodes_used)
         return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# layout B (RT-unit / "raytracing" host path): vxh_rtx_* of include/vortex_b200_host.h
+RTX_EXPORTS = ("vxh_rtx_scene_create vxh_rtx_scene_apply_transform vxh_rtx_scene_build vxh_rtx_scene_view vxh_rtx_scene_free "
+               "vxh_rtx_setup").split()
+RTX_BUFFERS = ("tri", "triEx", "triIdx", "mat", "tex", "bvh", "qbvh", "blas", "tlas")
+MATERIAL_DT = np.dtype([  # tests/regression/raytracing/common.h:20-36
+    ("ambient", "<f4", 3), ("diffuse", "<f4", 3), ("specular", "<f4", 3), ("emissive", "<f4", 3),
+    ("shininess", "<f4"), ("ior", "<f4"), ("dissolve", "<f4"), ("reflectivity", "<f4"),
+    ("diffuse_tex_id", "<i4"), ("illum", "<i4"), ("tex_width", "<u4"), ("tex_height", "<u4"), ("tex_offset", "<u8"),
+])
+assert MATERIAL_DT.itemsize == 88
+
+
+class _RtxView(C.Structure):
+    _fields_ = [(n, t) for name in RTX_BUFFERS for (n, t) in ((name, C.c_void_p), (name + "_bytes", C.c_uint64))] + \
+               [("tlas_root", C.c_uint32), ("bvh_nodes_used", C.c_uint32), ("tlas_nodes_used", C.c_uint32), ("_pad", C.c_uint32)]
+
+
+def _rtx_lib():
+    L = lib()
+    if not getattr(L, "_rtx_ready", False):
+        L.vxh_rtx_scene_create.restype = C.c_void_p
+        L.vxh_rtx_scene_create.argtypes = [C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint64, C.c_void_p, C.c_void_p, C.c_int]
+        L.vxh_rtx_scene_apply_transform.argtypes = [C.c_void_p, C.c_void_p]
+        L.vxh_rtx_scene_build.argtypes = [C.c_void_p]
+        L.vxh_rtx_scene_view.argtypes = [C.c_void_p, C.POINTER(_RtxView)]
+        L.vxh_rtx_scene_free.argtypes = [C.c_void_p]
+        L.vxh_rtx_setup.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_float,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        for n in RTX_EXPORTS[1:]:
+            getattr(L, n).restype = None
+        L._rtx_ready = True
+    return L
+
+
+class RtxHostScene:
+    """meshes: list of dict(tris (n,9) f32, triex (n,15) f32, texid (n,) u32 [material index local to the mesh],
+    materials: list of dict(diffuse=(r,g,b) | tex=(h,w) u32), reflectivity, transform (4,4) | None)."""
+
+    def __init__(self, meshes, threads=0):
+        from .rtx_tracer import KARG_B_DT
+        self._karg_dt = KARG_B_DT
+        counts = np.array([m["tris"].shape[0] for m in meshes], dtype=np.uint32)
+        tris = np.ascontiguousarray(np.concatenate([m["tris"].reshape(-1, 9) for m in meshes]), dtype=np.float32)
+        ex = []
+        for m in meshes:
+            n = m["tris"].shape[0]
+            rec = np.zeros((n, 16), dtype=np.uint32)
+            rec[:, :15] = np.ascontiguousarray(m["triex"].reshape(n, 15), dtype=np.float32).view(np.uint32)
+            rec[:, 15] = np.asarray(m.get("texid", np.zeros(n, np.uint32)), dtype=np.uint32)
+            ex.append(rec)
+        triex = np.ascontiguousarray(np.concatenate(ex))
+        n_mats = np.array([len(m["materials"]) for m in meshes], dtype=np.uint32)
+        mats = np.zeros(int(n_mats.sum()), dtype=MATERIAL_DT)
+        chunks, off, k = [], 0, 0
+        for m in meshes:
+            for mat in m["materials"]:
+                mats[k]["diffuse"] = mat.get("diffuse", (0.8, 0.8, 0.8))
+                mats[k]["ambient"], mats[k]["dissolve"] = (0.1, 0.1, 0.1), 1.0
+                t = mat.get("tex")
+                if t is not None:
+                    t = np.ascontiguousarray(t, dtype=np.uint32)
+                    mats[k]["diffuse_tex_id"] = 0
+                    mats[k]["tex_width"], mats[k]["tex_height"], mats[k]["tex_offset"] = t.shape[1], t.shape[0], off
+                    chunks.append(t.reshape(-1).view(np.uint8))
+                    off += t.size * 4
+                else:
+                    mats[k]["diffuse_tex_id"] = -1
+                k += 1
+        tex = np.ascontiguousarray(np.concatenate(chunks)) if chunks else np.zeros(0, np.uint8)
+        refl = np.array([m.get("reflectivity", 0.0) or 0.0 for m in meshes], dtype=np.float32)
+        tr = None
+        if any(m.get("transform") is not None for m in meshes):
+            tr = np.ascontiguousarray(np.stack([np.asarray(m["transform"], dtype=np.float32) if m.get("transform") is not None
+                                                else np.eye(4, dtype=np.float32) for m in meshes]), dtype=np.float32)
+        self.h = _rtx_lib().vxh_rtx_scene_create(len(meshes), counts.ctypes.data, tris.ctypes.data, triex.ctypes.data, n_mats.ctypes.data,
+                                                 mats.ctypes.data if len(mats) else None, tex.ctypes.data if len(tex) else None, len(tex),
+                                                 refl.ctypes.data, tr.ctypes.data if tr is not None else None, threads)
+        if not self.h:
+            raise RuntimeError("vxh_rtx_scene_create failed")
+        self.karg = None
+
+    def __del__(self):
+        try:
+            if self.h:
+                _rtx_lib().vxh_rtx_scene_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def apply_transform(self, m):
+        """Scene::applyTransform (raytracing/scene.cpp:247-251)"""
+        m = np.ascontiguousarray(np.asarray(m, dtype=np.float32).reshape(16))
+        _rtx_lib().vxh_rtx_scene_apply_transform(self.h, m.ctypes.data)
+
+    def setup(self, width, height, spp=1, max_depth=1, vfov=45.0, zoom=1.0, light_pos=DEFAULT_LIGHT_POS,
+              light_color=DEFAULT_LIGHT_COLOR, ambient=DEFAULT_AMBIENT, background=DEFAULT_BACKGROUND):
+        buf = np.zeros(1, dtype=self._karg_dt)
+        _rtx_lib().vxh_rtx_setup(self.h, buf.ctypes.data, width, height, spp, max_depth, vfov, zoom, _f3(light_pos), _f3(light_color),
+                                 _f3(ambient), _f3(background))
+        self.karg = buf
+        return buf
+
+    def buffers(self):
+        v = _RtxView()
+        _rtx_lib().vxh_rtx_scene_view(self.h, C.byref(v))
+        out = {}
+        for n in RTX_BUFFERS:
+            nbytes = getattr(v, n + "_bytes")
+            out[n] = np.frombuffer(C.string_at(getattr(v, n), nbytes), dtype=np.uint8).copy() if nbytes else np.zeros(0, np.uint8)
+        out["bvh_nodes_used"], out["tlas_nodes_used"] = int(v.bvh_nodes_used), int(v.tlas_nodes_used)
+        return out
