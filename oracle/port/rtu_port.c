@@ -41,6 +41,14 @@ typedef struct {
 } rtu_node;
 #pragma pack(pop)
 
+/* The reference computes child addresses from `base_ptr`, which BVHTraverser::pop does NOT reset when the popped entry is a
+ * TLAS node (rt_traversal.cpp:179-213,92): after an instance was visited, the children of a popped TLAS *inner* node are
+ * fetched relative to that instance's BVH — geometry behind a TLAS of more than one inner level is silently missed.
+ * 0 (default) reproduces this; 1 addresses the children of TLAS nodes from the TLAS base (what the author evidently meant),
+ * used only to check the CUDA fast order, which has no such defect. */
+static int g_fix_tlas_base = 0;
+void port_rtu_set_fix_tlas_base(int on) { g_fix_tlas_base = on; }
+
 static void img_read(const rtu_image *im, void *dst, uint64_t addr, uint32_t n) {   /* RTUnit::dcache_read */
   if (addr < im->base || addr + n > im->base + im->size) { memset(dst, 0, n); return; }
   memcpy(dst, im->mem + (addr - im->base), n);
@@ -174,6 +182,7 @@ static int traverse(const rtu_image *im, const rtu_ray *ray, rtu_hit *hit, float
       } else {
         uint32_t closest = idx[n - 1];
         n--;
+        if (g_fix_tlas_base && is_top(&node)) base_ptr = im->tlas;
         node_ptr = base_ptr + (node.leftFirst + closest) * RTU_NODE_BYTES;
         if (n == 0) trail[level] = RTU_WIDTH;
         else

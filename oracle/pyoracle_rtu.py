@@ -219,6 +219,12 @@ class RtuPort:
         L.port_rtuh_render.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                        C.c_uint32, C.c_void_p]
         L.port_rtuh_primary_rays.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.port_rtu_set_fix_tlas_base.argtypes = [C.c_int]
+
+    def set_fix_tlas_base(self, on):
+        """0 (default): reproduce the reference's stale-base_ptr defect on popped TLAS inner nodes (rt_traversal.cpp:179-213);
+        1: address TLAS children from the TLAS base.  See oracle/port/rtu_port.c."""
+        self.lib.port_rtu_set_fix_tlas_base(int(bool(on)))
 
     def trace_rays(self, img, rays, threads=1, want_work=False, want_wrap_flags=False):
         """want_wrap_flags: also return one byte per ray, 1 where traversal reaches the reference's `size()-1` wrap

@@ -33,18 +33,28 @@ def load_golden(path):
 def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
     port = R.RtuPort()
     img = R.Image(bufs, karg)
+    threads = os.cpu_count() or 1
     rays = port.primary_rays(img, cam)
     hits_port, work, flags = port.trace_rays(img, rays, want_work=True, want_wrap_flags=True)
-    frame_port, work_r = port.render(img, cam, threads=os.cpu_count() or 1, want_work=True)
+    frame_port, work_r = port.render(img, cam, threads=threads, want_work=True)
+    # The reference addresses the children of a popped TLAS inner node from a stale base_ptr (rt_traversal.cpp:179-213) and so
+    # misses geometry behind TLASes of more than one inner level.  Strict order reproduces that address for address; the fast
+    # order does not have the defect and is checked against the port with the base fixed (oracle/port/rtu_port.c).
+    port.set_fix_tlas_base(1)
+    try:
+        hits_fix = port.trace_rays(img, rays, threads=threads)
+        frame_fix = port.render(img, cam, threads=threads)
+    finally:
+        port.set_fix_tlas_base(0)
     tr = tracer_b(bufs, karg, cam)
     try:
         tr.dev.enable_stats(True)
         for strict in (1, 0):
             tr.set_order(strict)
+            want_hits, want_frame = (hits_port, frame_port) if strict else (hits_fix, frame_fix)
             hits = tr.trace_primary()
             st = tr.dev.stats()
-            hp = hit_parity(hits, hits_port)
-            assert_hit_gates(hp, strict)
+            assert_hit_gates(hit_parity(hits, want_hits), strict)
             if strict:
                 assert hits.tobytes() == hits_port.tobytes()
                 # work counters of the reference algorithm: node reads, instance entries, triangle tests
@@ -52,17 +62,17 @@ def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
             # caller-supplied rays take the same path
             assert tr.trace_rays(rays).tobytes() == hits.tobytes()
             frame = tr.run()
-            d = channel_diff(frame, frame_port)
-            assert d <= (0 if strict else 1), d
+            d = channel_diff(frame, want_frame)
+            assert d <= (0 if strict else 1), (strict, d, int((frame != want_frame).sum()))
             if strict:
                 assert np.array_equal(frame, frame_port)
                 assert tr.dev.stats()["shaded_hits"] == work_r["shaded_hits"]
-            if ref_hits is not None:   # outputs of the compiled reference recorded in the fixture
-                assert_hit_gates(hit_parity(hits, ref_hits), strict)
-                assert channel_diff(frame, ref_image) <= (0 if strict else 1)
+                if ref_hits is not None:   # outputs of the compiled reference recorded in the fixture
+                    assert hits.tobytes() == ref_hits.tobytes()
+                    assert np.array_equal(frame, ref_image)
         if R.have_ref():
             ok = flags == 0
-            h_ref = R.RtuRef().trace_rays(img, rays[ok], threads=os.cpu_count() or 1)
+            h_ref = R.RtuRef().trace_rays(img, rays[ok], threads=threads)
             tr.set_order(1)
             assert tr.trace_rays(rays[ok]).tobytes() == h_ref.tobytes()
     finally:
@@ -104,6 +114,8 @@ def test_rtu_full_size_fast_equals_strict():
     from rtu_common import b_mesh
     host = importlib.import_module("vortex-raytracing_b200.host")
     hs = host.RtxHostScene([b_mesh(scenes.heightfield(224))])
+    c = np.float32(np.cos(np.pi / 4))   # look down on the terrain: RotateX(-pi/4), as the raycast host does (raycast/tracer.cpp:157)
+    hs.apply_transform(np.array([[1, 0, 0, 0], [0, c, c, 0], [0, -c, c, 0], [0, 0, 0, 1]], dtype=np.float32))
     karg = hs.setup(1920, 1080)
     tr = tracer_b(hs.buffers(), karg, 1)
     try:

@@ -262,7 +262,7 @@ constexpr uint32_t kLastBit = 0x40000000u;
 constexpr uint32_t kTrailLevels = 32;   // MAX_TRAIL_LEVEL
 
 // BVHTraverser::pop (:179-213).  Returns true when traversal is complete.
-__device__ __forceinline__ bool strict_pop(uint32_t &cur, uint32_t &level, uint8_t *trail, Ring &stack) {
+__device__ __forceinline__ bool strict_pop(uint32_t &cur, uint32_t &base, uint32_t &level, uint8_t *trail, Ring &stack) {
   int parent = -1;
   for (int i = (int)level - 1; i >= 0; i--)
     if (trail[i] != 4) {
@@ -273,7 +273,8 @@ __device__ __forceinline__ bool strict_pop(uint32_t &cur, uint32_t &level, uint8
   trail[parent]++;
   for (uint32_t i = parent + 1; i < kTrailLevels; i++) trail[i] = 0;
   if (stack.count == 0) {
-    cur = kTlasBit | 0u;   // restart from the root
+    cur = kTlasBit | 0u;   // restart from the root (base_ptr = node_ptr = tlas_ptr)
+    base = kTlasBit | 0u;
     level = 0;
   } else {
     uint32_t e = ring_pop(stack);
@@ -290,18 +291,24 @@ __device__ __forceinline__ bool strict_traverse(const RtuScene &sc, const Ray &w
                                                 uint8_t *trail, Ring &stack, Local &lc) {
   uint32_t level = 0;
   uint32_t cur = kTlasBit | 0u;
+  // `base` is the reference's base_ptr as (buffer, node index): child k of a node lives at base + leftFirst + k.  pop()
+  // does NOT restore it when the popped entry is a TLAS node (:179-213), so after an instance was visited the children
+  // of a popped TLAS inner node are fetched from that instance's BVH.  Reproduced here address for address; the node's own
+  // imask (not the buffer it was fetched from) decides how it is interpreted, as in the reference.
+  uint32_t base = kTlasBit | 0u;
   Instance in;
   in.base = 0, in.blasIdx = 0, in.ray = world;
   bool done = false;
   while (!done) {
-    const bool top = (cur & kTlasBit) != 0;
+    const bool in_tlas_buf = (cur & kTlasBit) != 0;
     const uint32_t idx = cur & ~kTlasBit;
-    if (!(top ? (idx < sc.n_tlas) : (idx < sc.n_bvh))) {   // hostile index: treat as an empty inner node
-      done = strict_pop(cur, level, trail, stack);
+    if (!(in_tlas_buf ? (idx < sc.n_tlas) : (idx < sc.n_bvh))) {   // hostile index: treat as an empty inner node
+      done = strict_pop(cur, base, level, trail, stack);
       continue;
     }
-    const GpuNodeB *n = (top ? sc.gtlas : sc.gbvh) + idx;
+    const GpuNodeB *n = (in_tlas_buf ? sc.gtlas : sc.gbvh) + idx;
     uint4 info = load_info(n);
+    const bool top = (info.z & kFlagTlas) != 0;
     if (STATS) lc.box++;
     if (!(info.z & kFlagLeaf)) {
       NodeBoxes b = load_boxes(n);
@@ -328,10 +335,10 @@ __device__ __forceinline__ bool strict_traverse(const RtuScene &sc, const Ray &w
       uint32_t drop = (k == 4) ? (cnt > 0 ? (uint32_t)cnt - 1 : 0) : k;   // :80-86 (the size()-1 wrap on an empty list drops nothing)
       while (drop-- > 0 && cnt > 0) cnt--;
       if (cnt == 0) {
-        done = strict_pop(cur, level, trail, stack);
+        done = strict_pop(cur, base, level, trail, stack);
       } else {
-        const uint32_t space = top ? kTlasBit : 0u;
-        const uint32_t child0 = (top ? 0u : in.base) + info.x;
+        const uint32_t space = base & kTlasBit;
+        const uint32_t child0 = (base & ~kTlasBit) + info.x;
         uint32_t closest = ci[cnt - 1];
         cnt--;
         cur = space | (child0 + closest);
@@ -346,15 +353,16 @@ __device__ __forceinline__ bool strict_traverse(const RtuScene &sc, const Ray &w
       if (enter_instance(sc, wray, info.y, in)) {
         if (STATS) lc.blas++;
         cur = in.base;
+        base = in.base;
       } else {
-        done = strict_pop(cur, level, trail, stack);
+        done = strict_pop(cur, base, level, trail, stack);
       }
     } else {
       if (leaf_tris<STATS, true>(sc, info.x, info.y, in.ray, in.blasIdx, hit, pending, lc)) {
         stack.count = 0, stack.head = 0;   // "clear stack for now to ensure correctness" (:148-152)
         return false;
       }
-      done = strict_pop(cur, level, trail, stack);
+      done = strict_pop(cur, base, level, trail, stack);
     }
   }
   return true;
