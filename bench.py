@@ -33,6 +33,11 @@ WORKLOADS = {
     "cfg3_8k_primary+shadow_1m": dict(n=708, w=7680, h=4320, mode=1, depth=1, config_index=3),
     "primary_4k_1m": dict(n=708, w=3840, h=2160, mode=0, depth=1, config_index=None),
     "cfg0_cornell64_primary": dict(n=0, w=64, h=64, mode=0, depth=1, config_index=0),
+    # BASELINE configs[4]: incoherent random-direction rays, 10 M triangles, rays sharded by index (2^23 per GPU = 2^26 on 8)
+    # geometry scaled x4: at 10 M triangles over [-1,1]^2 the Moller-Trumbore determinant |a| ~ 2*area falls below the reference's
+    # EPSILON = 1e-6 "parallel ray" rejection (geometry.h:1424) and 96 % of the triangles become invisible to the reference itself
+    "cfg4_incoherent_10m": dict(n=2237, w=8, h=8, mode=0, depth=1, config_index=4, rays_per_gpu=1 << 23, scale=4.0),
+    "incoherent_1m": dict(n=708, w=8, h=8, mode=0, depth=1, config_index=None, rays_per_gpu=1 << 23),
 }
 METRIC = "Mrays/s (primary + shadow + bounce rays, whole job)"
 BAND_ROWS = 8
@@ -44,7 +49,12 @@ def pkg(name):
 
 def make_meshes(wl):
     scenes = pkg("scenes")
-    return [scenes.cornell_box()] if wl["n"] == 0 else [scenes.heightfield(wl["n"])]
+    if wl["n"] == 0:
+        return [scenes.cornell_box()]
+    m = scenes.heightfield(wl["n"])
+    if wl.get("scale", 1.0) != 1.0:
+        m["tris"] = (m["tris"] * np.float32(wl["scale"])).astype(np.float32)
+    return [m]
 
 
 def peaks():
@@ -142,7 +152,23 @@ def run_reference(args, wl, name):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    frame, kind, threads, sample = cpu_frame_timer(wl, budget_s=max(2.0, 150.0 / max(1, args.steps + args.warmup)))
+    if "rays_per_gpu" in wl:      # incoherent-ray workload: the reference's TLASIntersect over a bounded sample of the same ray set
+        orc, kind = cpu_oracle()
+        sc = orc.scene_create(make_meshes(wl))
+        sc.setup(wl["w"], wl["h"], spp=1, max_depth=1)
+        threads = orc.hw_threads()
+        n_s = 1 << 18
+        sc_ = np.float32(wl.get("scale", 1.0))
+        rays = pkg("scenes").random_rays(n_s, tuple(sc_ * np.float32(v) for v in (-1.0, -0.05, -1.0)),
+                                         tuple(sc_ * np.float32(v) for v in (1.0, 0.45, 1.0)), seed=1, start=0)
+
+        def frame():
+            t = time.perf_counter()
+            sc.trace_rays(rays, threads=threads)
+            return time.perf_counter() - t, n_s
+        sample = f"first {n_s} rays of the global ray set, all host threads"
+    else:
+        frame, kind, threads, sample = cpu_frame_timer(wl, budget_s=max(2.0, 150.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         frame()
     tot_t, tot_r = 0.0, 0
@@ -337,6 +363,158 @@ def run_b200(args, wl, name):
         dist.destroy_process_group()
 
 
+def run_incoherent(args, wl, name):
+    """BASELINE configs[4]: closest-hit records of incoherent rays through vx_b200_trace_rays.  Rays are sharded by
+    index (rank r traces rays [r*R, (r+1)*R) of one global WangHash-seeded set), the scene is replicated, no data-path collective:
+    weak scaling.  value = rays of all ranks / max-over-ranks device time with rays and scene resident in HBM; e2e adds the
+    host->device copy of the rays and the device->host copy of the hit records every step."""
+    import torch
+    import torch.distributed as dist
+
+    vx, tracer_mod, host, scenes = pkg("vx"), pkg("tracer"), pkg("host"), pkg("scenes")
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: the b200 backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    R = int(wl["rays_per_gpu"])
+    t0 = time.perf_counter()
+    hs = host.HostScene(make_meshes(wl))
+    karg = hs.setup(wl["w"], wl["h"], spp=1, max_depth=1)
+    bufs = hs.buffers()
+    build_s = time.perf_counter() - t0
+    tr = tracer_mod.Tracer(wl["w"], wl["h"], 1, 1, cuda_device=local).init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names})
+    tr.set_mode(0, 0)
+    tr._upload_args()
+    sc_ = np.float32(wl.get("scale", 1.0))
+    rays = scenes.random_rays(R, tuple(sc_ * np.float32(v) for v in (-1.0, -0.05, -1.0)), tuple(sc_ * np.float32(v) for v in (1.0, 0.45, 1.0)),
+                              seed=1, start=rank * R)   # the scene's AABB, a little headroom above
+    rays_pinned = torch.from_numpy(rays).pin_memory()
+    hits_pinned = torch.empty(R * 24, dtype=torch.uint8).pin_memory()
+    rb = tr.dev.mem_alloc(R * 24)
+    hb = tr.dev.mem_alloc(R * 24)
+    rb.copy_to_dev((rays_pinned.data_ptr(), R * 24))
+    ext = torch.cuda.ExternalStream(tr.dev.stream(), device=torch.device("cuda", local))
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")
+
+    def step(ev=None):
+        with torch.cuda.stream(ext):
+            flush.zero_()
+            if ev:
+                ev[0].record()
+            tr.dev.trace_rays(tr.args, rb, R, hb)
+            if ev:
+                ev[1].record()
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    sync_all()
+    tr.dev.ready_wait()
+    sampler = ClockSampler(local) if rank == 0 else None
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kernel_ms = []
+    for e in evs:
+        step(e)
+        tr.dev.ready_wait()
+        kernel_ms.append(tr.dev.last_kernel_ms())
+    sync_all()
+    clocks = sampler.stop() if sampler else None
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    launches_per_step = tr.dev.stats()["kernel_launches"]
+    t_ms = torch.tensor([total_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(t_ms.item())
+    rays_step = R * world
+    value = rays_step * args.steps / (total_ms * 1e3)
+
+    def e2e_step():
+        rb.copy_to_dev((rays_pinned.data_ptr(), R * 24))
+        tr.dev.trace_rays(tr.args, rb, R, hb)
+        tr.dev.ready_wait()
+        hb.copy_from_dev((hits_pinned.data_ptr(), R * 24))
+
+    e2e_steps = max(3, min(args.steps, 5))
+    e2e_step()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = rays_step * e2e_steps / float(e2e_s.item()) / 1e6
+    hits = np.frombuffer(hits_pinned.numpy().tobytes(), dtype=tracer_mod.HIT_DT)
+    hit_frac = float((hits["dist"] < 1e30).mean())
+
+    tr.set_mode(0, 1)                      # strict order = the reference's visiting order => its algorithmic work
+    tr.dev.enable_stats(True)
+    tr.dev.trace_rays(tr.args, rb, R, hb)
+    tr.dev.ready_wait()
+    work = tr.dev.stats()
+    tr.dev.enable_stats(False)
+    tr.set_mode(0, 0)
+    abytes = 32 * work["box_tests"] + 40 * work["tri_tests"] + 160 * work["blas_entered"] + 48 * R    # + ray in (24 B) and hit record out (24 B)
+    aflops = 27 * work["box_tests"] + 53 * work["tri_tests"] + 30 * work["blas_entered"]
+    k_ms = float(np.mean(kernel_ms))
+    hbm, hbm_src, sm_mhz = peaks()
+    achieved = abytes / (k_ms * 1e-3) / 1e9
+    fp32_peak = tr.dev.caps(0x3) * 128 * 2 * sm_mhz * 1e6 / 1e12
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        po = importlib.import_module("oracle.pyoracle")
+        orc, kind = cpu_oracle()
+        raw = po.RawScene(orc, bufs, karg)       # the oracle's hot loop on the very bytes that were uploaded
+        sample = rays[: 1 << 18]
+        threads = orc.hw_threads()
+        best = None
+        for _ in range(2):
+            t0 = time.perf_counter()
+            ref_hits = raw.trace_rays(sample, threads=threads)
+            dt = time.perf_counter() - t0
+            best = dt if best is None or dt < best else best
+        same = (ref_hits["triIdx"] == hits["triIdx"][: len(sample)]) & (ref_hits["dist"] == hits["dist"][: len(sample)])
+        cpu = {"value": len(sample) / best / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
+               "sample": f"first {len(sample)} rays of rank 0's shard, all host threads, best of 2",
+               "gpu_hit_records_identical_on_sample": float(same.mean())}
+    if rank == 0:
+        ntri = 2 * wl["n"] ** 2
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": name, "baseline_config_index": wl["config_index"], "triangles": ntri, "scene_scale": wl.get("scale", 1.0), "rays_per_gpu": R,
+                           "rays_per_step": rays_step, "hit_fraction": hit_frac,
+                           "partition": f"rays sharded by index over {world} GPU(s), scene replicated, no collective on the data path",
+                           "l2": "512 MB memset between timed iterations (L2 flush); working set (scene 1.6 GB at 10 M triangles) >> L2",
+                           "host_bvh_build_s": round(build_s, 3)},
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 24, "steps": e2e_steps,
+                        "timer": "host wall clock around vx_copy_to_dev(rays) + vx_b200_trace_rays + vx_ready_wait + vx_copy_from_dev(hits), max over ranks"},
+                "gpu_launches": int(launches_per_step) * args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
+                             "peak_source": hbm_src, "kernel": "k_trace_a", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes,
+                             "algorithmic_bytes_per_ray": abytes / R,
+                             "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
+                                      "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},
+                             "work_per_ray": {k: work[k] / R for k in ("box_tests", "tri_tests", "blas_entered")}},
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    tr.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def quick_run(name, local, steps=5, kernel=0):
     """kernel-only Mrays/s of another workload on one GPU (reported under config.extra_workloads; not the headline)."""
     tracer_mod, host = pkg("tracer"), pkg("host")
@@ -437,6 +615,8 @@ def main():
     wl = WORKLOADS[name]
     if args.impl == "reference":
         run_reference(args, wl, name)
+    elif "rays_per_gpu" in wl:
+        run_incoherent(args, wl, name)
     else:
         run_b200(args, wl, name)
 

@@ -190,10 +190,11 @@ def icosphere(center, radius, subdiv=2, tex=None, reflectivity=0.0):
     return {"tris": tris, "triex": triex, "tex": tex, "reflectivity": float(reflectivity)}
 
 
-def random_rays(n, bmin, bmax, seed=1):
+def random_rays(n, bmin, bmax, seed=1, start=0):
     """Incoherent rays (config 5): origin uniform in the box, direction uniform on the sphere
-    (z = 1 - 2 u1, phi = 2 pi u2), all from WangHash(i)-seeded integers.  Returns (n,6) float32."""
-    i = np.arange(n, dtype=np.uint32)
+    (z = 1 - 2 u1, phi = 2 pi u2), all from WangHash(i)-seeded integers; ray indices start .. start+n-1 (so that ranks
+    can generate their own shard of one global ray set).  Returns (n,6) float32."""
+    i = np.arange(start, start + n, dtype=np.uint64).astype(np.uint32)
     inv = np.float32(1.0 / (1 << 24))
 
     def u(k):
