@@ -25,6 +25,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":   # keeps NCCL's banner off stdout: rank 0 prints ONE JSON line
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 WORKLOADS = {
     # name: heightfield quads per side, width, height, mode (bit0 shadow, bit1 diffuse bounces), max_depth
@@ -220,13 +222,38 @@ def run_b200(args, wl, name):
     fb = mg.framebuffer_tensor(tr, local)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")       # > 126 MB L2
 
+    # N > 1: by default the ranks' kernels store their bands straight into rank 0's framebuffer over NVLink peer memory
+    # (--gather p2p); --gather nccl renders locally and moves the bands with one NCCL gather inside the timed region.
+    p2p = world > 1 and args.gather == "p2p"
+    check = {}
+    if world > 1:   # both transports must deliver the same frame to rank 0
+        tr.dev.start(tr.krnl, tr.args)
+        with torch.cuda.stream(ext):
+            mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
+        ext.synchronize()
+        tr.dev.ready_wait()
+        ref_frame = fb.clone() if rank == 0 else None
+        if rank == 0:
+            fb.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        mg.share_framebuffer(tr, rank, world)
+        tr.dev.start(tr.krnl, tr.args)
+        tr.dev.ready_wait()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            check["p2p_frame_equals_nccl_gather_frame"] = bool(torch.equal(fb, ref_frame))
+        if not p2p:
+            mg.unshare_framebuffer(tr, rank, world)
+
     def step(timed_events=None):
         with torch.cuda.stream(ext):
             flush.zero_()                                       # L2 flush between iterations, outside the timed pair
             if timed_events:
                 timed_events[0].record()
             tr.dev.start(tr.krnl, tr.args)                      # vx_start: async, on the same CUDA stream
-            if world > 1:
+            if world > 1 and not p2p:
                 mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
             if timed_events:
                 timed_events[1].record()
@@ -272,11 +299,13 @@ def run_b200(args, wl, name):
             tr.bufs[n].copy_to_dev((t.data_ptr(), t.numel()))
         tr._upload_args()
         tr.dev.start(tr.krnl, tr.args)
-        if world > 1:
+        if world > 1 and not p2p:
             with torch.cuda.stream(ext):
                 mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
             ext.synchronize()
         tr.dev.ready_wait()
+        if p2p:
+            dist.barrier()          # every rank's bands have landed in rank 0's framebuffer
         if rank == 0:
             tr.out.copy_from_dev((out_pinned.data_ptr(), W * H * 4))
 
@@ -342,6 +371,9 @@ def run_b200(args, wl, name):
                 "config": {"workload": name, "baseline_config_index": wl["config_index"], "width": W, "height": H,
                            "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32, "mode": wl["mode"], "max_depth": wl["depth"],
                            "rays_per_step": rays_step, "partition": f"{BAND_ROWS}-row bands round-robin over {world} GPU(s), scene replicated",
+                           "framebuffer_transport": ("none (single GPU)" if world == 1 else
+                                                     "kernels store into rank 0's framebuffer over NVLink peer memory (CUDA IPC)" if p2p else
+                                                     "NCCL gather inside the timed region"), **check,
                            "l2": "512 MB memset between timed iterations (L2 flush); timed per step with CUDA events on the launch stream",
                            "host_bvh_build_s": round(build_s, 3), "extra_workloads": extra},
                 "clocks": clocks,
@@ -609,6 +641,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--kernel", type=int, default=0, help="layout-A render kernel: 0 = ray state machine (default), 1 = one pixel per lane")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: how the bands reach rank 0's framebuffer")
     ap.add_argument("--extra", type=int, default=1, help="also report kernel-only numbers of the 1M-triangle workloads (N=1)")
     args = ap.parse_args()
     name = args.workload or ("cfg1_1080p_primary+shadow_100k" if args.gpus == 1 else "cfg3_8k_primary+shadow_1m")

@@ -144,6 +144,15 @@ int vx_b200_select_device(int cuda_device);
  * world == 1 (default) renders everything.  Env defaults: VORTEX_B200_RANK / VORTEX_B200_WORLD. */
 int vx_b200_set_partition(vx_device_h hdevice, uint32_t rank, uint32_t world, uint32_t band_rows);
 
+/* Multi-GPU framebuffer over NVLink peer memory (one process per GPU).  The owner of the final image exports its framebuffer
+ * buffer (a CUDA IPC handle of the device arena + the buffer's offset in it); every other rank passes that to
+ * vx_b200_set_remote_framebuffer, after which its render kernels store their bands' pixels DIRECTLY into the owner's
+ * framebuffer over NVLink/NVSwitch while they trace (no separate gather step, no staging copy).  The image is complete on
+ * the owner once every rank's vx_ready_wait has returned (synchronise the ranks, e.g. a barrier, before reading it).
+ * handle == NULL detaches.  `bytes` must cover width*height*4 of every later vx_start. */
+int vx_b200_export_buffer(vx_buffer_h hbuffer, void *ipc_handle_64, uint64_t *offset);
+int vx_b200_set_remote_framebuffer(vx_device_h hdevice, const void *ipc_handle_64, uint64_t offset, uint64_t bytes);
+
 /* Raw CUDA device pointer behind a Vortex buffer (for NCCL / torch interop on the same process). */
 int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr);
 

@@ -100,6 +100,8 @@ public:
     if (cuda_dev_ < 0) return;
     cudaSetDevice(cuda_dev_);
     if (stream_) cudaStreamSynchronize(stream_);
+    if (remote_base_) cudaIpcCloseMemHandle(remote_base_);
+    remote_base_ = nullptr, remote_fb_ = nullptr;
     if (gtri_) cudaFree(gtri_);
     if (rtu_nodes_) cudaFree(rtu_nodes_);
     if (rtu_tri_) cudaFree(rtu_tri_);
@@ -291,6 +293,27 @@ public:
     part_.rank = rank, part_.world = world, part_.band_rows = band_rows;
     return 0;
   }
+  int set_remote_framebuffer(const void *handle, uint64_t offset, uint64_t bytes) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    if (run_pending_) {
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+    }
+    if (remote_base_) {
+      cudaIpcCloseMemHandle(remote_base_);
+      remote_base_ = nullptr, remote_fb_ = nullptr, remote_bytes_ = 0;
+    }
+    if (!handle) return 0;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *base = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    remote_base_ = base;
+    remote_fb_ = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(base) + offset);
+    remote_bytes_ = bytes;
+    return 0;
+  }
   uint8_t *arena() const { return arena_; }
   cudaStream_t stream() const { return stream_; }
   int cuda_device() const { return cuda_dev_; }
@@ -397,6 +420,10 @@ private:
     const float *rays = nullptr;
     if (!trace) {
       if (resolve(a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, 4, "framebuffer", &out)) return -1;
+      if (remote_fb_) {   // store this rank's bands straight into the image owner's framebuffer (peer memory)
+        if (remote_bytes_ < (uint64_t)a.dst_width * a.dst_height * 4) return fail("remote framebuffer smaller than the image");
+        out = remote_fb_;
+      }
     } else {
       uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
       if (resolve(*hits_addr, n * sizeof(HitA), 4, "hits", &hits)) return -1;
@@ -510,6 +537,10 @@ private:
     if (a.dst_width == 0 || a.dst_height == 0) return fail("empty framebuffer");
     RtuRender p{};
     if (resolve(a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, 4, "framebuffer", &p.out)) return -1;
+    if (remote_fb_) {
+      if (remote_bytes_ < (uint64_t)a.dst_width * a.dst_height * 4) return fail("remote framebuffer smaller than the image");
+      p.out = remote_fb_;
+    }
     if (begin_run_locked() != 0) return -1;
     if (rtu_scene_locked(a, &p.scene)) return -1;
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
@@ -551,6 +582,10 @@ private:
   std::unordered_map<uint64_t, std::vector<uint8_t>> small_shadow_;   // host copies of small uploads (argument blocks)
   std::unordered_map<uint32_t, uint32_t> dcrs_;
   Partition part_;
+  // framebuffer of the image owner, mapped over NVLink (vx_b200_set_remote_framebuffer)
+  void *remote_base_ = nullptr;
+  uint32_t *remote_fb_ = nullptr;
+  uint64_t remote_bytes_ = 0;
   // layout-A GPU triangle records
   GpuTri *gtri_ = nullptr;
   uint64_t gtri_cap_ = 0, gtri_slots_ = 0;
@@ -815,6 +850,22 @@ VXB_EXPORT int vx_b200_select_device(int cuda_device) {
 VXB_EXPORT int vx_b200_set_partition(vx_device_h h, uint32_t rank, uint32_t world, uint32_t band_rows) {
   if (!h) return -1;
   return ((Device *)h)->set_partition(rank, world, band_rows);
+}
+VXB_EXPORT int vx_b200_export_buffer(vx_buffer_h hbuffer, void *ipc_handle_64, uint64_t *offset) {
+  if (!hbuffer || !ipc_handle_64 || !offset) return -1;
+  auto b = (Buffer *)hbuffer;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t");
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaSetDevice(b->device->cuda_device());
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, b->device->arena());
+  if (e != cudaSuccess) return fail("cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  memcpy(ipc_handle_64, &h, 64);
+  *offset = b->addr;
+  return 0;
+}
+VXB_EXPORT int vx_b200_set_remote_framebuffer(vx_device_h h, const void *ipc_handle_64, uint64_t offset, uint64_t bytes) {
+  if (!h) return -1;
+  return ((Device *)h)->set_remote_framebuffer(ipc_handle_64, offset, bytes);
 }
 VXB_EXPORT int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr) {
   if (!hbuffer || !cuda_ptr) return -1;

@@ -6,6 +6,8 @@ After the render each rank holds its own bands inside a full-size framebuffer; `
 bands into rank 0's framebuffer with ONE collective (torch.distributed gather: NCCL over NVLink on the GPU box, gloo in the
 CPU tests) so that the single-buffer vx_copy_from_dev contract of the reference host (raycast/tracer.cpp:239) still holds
 on rank 0.  There is no other data-path communication: rays are independent and the scene is read-only.
+`share_framebuffer` removes even that collective: non-owner ranks map the owner's framebuffer (CUDA IPC over NVLink/NVSwitch)
+and their kernels write into it directly, so the transfer overlaps the tracing tile by tile.
 """
 import numpy as np
 import torch
@@ -69,6 +71,25 @@ def gather_framebuffer(fb, rank, world, band_rows=8, group=None, dst=0):
     else:
         dist.gather(mine, gather_list=None, dst=dst, group=group)
     return fb
+
+
+def share_framebuffer(tracer, rank, world, owner=0, group=None):
+    """Peer-memory alternative to gather_framebuffer: rank `owner` exports its device framebuffer (CUDA IPC handle of its arena +
+    offset, vx_b200_export_buffer) and every other rank maps it (vx_b200_set_remote_framebuffer), after which their render
+    kernels store their bands' pixels straight into the owner's framebuffer over NVLink while they trace.  No collective
+    remains on the data path; the image is complete on `owner` once all ranks' vx_ready_wait returned (barrier before reading)."""
+    if world == 1:
+        return
+    payload = [tracer.out.ipc_export() if rank == owner else None]
+    dist.broadcast_object_list(payload, src=owner, group=group)
+    if rank != owner:
+        handle, offset = payload[0]
+        tracer.dev.set_remote_framebuffer(handle, offset, tracer.width * tracer.height * 4)
+
+
+def unshare_framebuffer(tracer, rank, world, owner=0):
+    if world > 1 and rank != owner:
+        tracer.dev.set_remote_framebuffer(None)
 
 
 class DeviceArray:

@@ -24,7 +24,7 @@ EXPORTS = (
     "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
-    "vx_b200_select_device vx_b200_set_partition vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_select_device vx_b200_set_partition vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
     "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_last_error"
 ).split()
 
@@ -64,6 +64,7 @@ def lib():
             "vx_b200_stream": [H, C.POINTER(u64)], "vx_b200_last_kernel_ms": [H, C.POINTER(C.c_float)],
             "vx_b200_enable_stats": [H, i32], "vx_b200_get_stats": [H, C.POINTER(Stats)],
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
+            "vx_b200_export_buffer": [B, vp, C.POINTER(u64)], "vx_b200_set_remote_framebuffer": [H, vp, u64, u64],
         }
         for name, args in sig.items():
             f = getattr(L, name)
@@ -108,6 +109,13 @@ class Buffer:
         v = C.c_uint64()
         _check(lib().vx_b200_device_ptr(self.h, C.byref(v)), "vx_b200_device_ptr")
         return v.value
+
+    def ipc_export(self):
+        """(64-byte CUDA IPC handle of the device arena, offset of this buffer in it) for vx_b200_set_remote_framebuffer"""
+        hb = C.create_string_buffer(64)
+        off = C.c_uint64()
+        _check(lib().vx_b200_export_buffer(self.h, hb, C.byref(off)), "vx_b200_export_buffer")
+        return hb.raw, off.value
 
     def copy_to_dev(self, host, dst_offset=0):
         p, n, _keep = _ptr(host)
@@ -197,6 +205,11 @@ class Device:
         return v.value
 
     # ---- b200 extensions ----
+    def set_remote_framebuffer(self, handle, offset=0, nbytes=0):
+        """handle: the 64 bytes of Buffer.ipc_export() from the image owner's process (None detaches)"""
+        hb = C.create_string_buffer(bytes(handle), 64) if handle is not None else None
+        _check(lib().vx_b200_set_remote_framebuffer(self.h, hb, C.c_uint64(offset), C.c_uint64(nbytes)), "vx_b200_set_remote_framebuffer")
+
     def set_partition(self, rank, world, band_rows=8):
         _check(lib().vx_b200_set_partition(self.h, rank, world, band_rows), "vx_b200_set_partition")
 
