@@ -23,6 +23,9 @@
 //     re-traversal after every accepted candidate) — used to prove arithmetic parity: hit records AND work counters
 //     equal the oracle's exactly;
 //   * persistent warps pull 8x4 screen tiles from an atomic counter; FP32 only, -fmad=false.
+//   * tried and rejected (measured on B200, 1080p / 100 K triangles): Aila-Laine "while-while" control flow (all lanes descend
+//     inner nodes until every lane holds a leaf) — 4.6 vs 6.9 Grays/s: with 4-wide nodes a ray visits only ~10 nodes, so
+//     waiting for the slowest lane's descent costs more than the leaf-phase convergence saves.
 #include <cstdio>
 #include "rt_device.cuh"
 #include "rt_rtu.h"
@@ -31,6 +34,9 @@ namespace vxb {
 namespace {
 using namespace dev;
 
+#ifndef VXB_RTU_MIN_BLOCKS
+#define VXB_RTU_MIN_BLOCKS 3
+#endif
 constexpr uint32_t kFlagTlas = 1u, kFlagLeaf = 2u;
 constexpr uint32_t kStackB = 96;          // fast-order stack entries (3 pushes per level at most)
 constexpr uint32_t kTlasBit = 0x80000000u;
@@ -508,7 +514,7 @@ __device__ __forceinline__ f3 shade_b(const RtuScene &sc, const KernelArgB &a, R
 
 // ---------------------------------------------------------------- the pixel loop (kernel.cpp:41-133)
 template <bool STRICT, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads) k_rtu_render(const __grid_constant__ RtuRender p) {
+__global__ void __launch_bounds__(kBlockThreads, STRICT ? 2 : VXB_RTU_MIN_BLOCKS) k_rtu_render(const __grid_constant__ RtuRender p) {
   uint32_t stk_e[STRICT ? 1 : kStackB];
   float stk_d[STRICT ? 1 : kStackB];
   const KernelArgB &a = p.arg;
