@@ -534,7 +534,7 @@ def run_incoherent(args, wl, name):
                         "timer": "host wall clock around vx_copy_to_dev(rays) + vx_b200_trace_rays + vx_ready_wait + vx_copy_from_dev(hits), max over ranks"},
                 "gpu_launches": int(launches_per_step) * args.steps,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                             "peak_source": hbm_src, "kernel": "k_trace_a", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes,
+                             "peak_source": hbm_src, "kernel": "k_render_m<trace> (ray state machine, rays as work items)", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes,
                              "algorithmic_bytes_per_ray": abytes / R,
                              "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
                                       "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},

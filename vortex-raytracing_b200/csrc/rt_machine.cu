@@ -265,12 +265,33 @@ __device__ __forceinline__ void begin_sample(Lane &L, const Smem &sm, const Rend
   start_ray(L, sm, p.scene, r.o, r.d, kLargeFloat, false, lc);
 }
 
+constexpr uint32_t kModeTrace = 4;   // work items are rays, POST writes the ray_hit_t record (vx_b200_trace_*)
+
+// hit-record mode: item `i` is ray i of the caller's buffer (or primary ray i)
+__device__ __forceinline__ void begin_trace(Lane &L, const Smem &sm, const RenderA &p, uint32_t i, Local &lc) {
+  Ray r;
+  if (p.rays) {
+    const float *q = p.rays + 6ull * i;
+    r.o = mk3(__ldg(q), __ldg(q + 1), __ldg(q + 2));
+    r.d = mk3(__ldg(q + 3), __ldg(q + 4), __ldg(q + 5));
+  } else {
+    r = generate_ray(i % p.arg.dst_width, i / p.arg.dst_width, p.arg);
+  }
+  start_ray(L, sm, p.scene, r.o, r.d, kLargeFloat, false, lc);
+}
+
 // POST: closest-hit shading / shadow resolution and the bounce loop of Trace (render.h:210-276) and of the extended
 // modes (shadow rays, diffuse bounces; same expressions as rt_raycast.cu:trace_ext and the CPU oracles' TraceExt)
 template <uint32_t MODE, bool STATS>
 __device__ __forceinline__ void post(Lane &L, const Smem &sm, const RenderA &p, Local &lc) {
   constexpr bool SHADOW = (MODE & 1u) != 0, DIFFUSE = (MODE & 2u) != 0;
   const KernelArgA &a = p.arg;
+  if (MODE == kModeTrace) {
+    const bool hit = L.dist != kLargeFloat;   // misses keep the all-zero record of render.h's ray_hit_t initialiser
+    p.hits[sm.u(C_PIX)] = HitA{L.dist, hit ? L.bx : 0.f, hit ? L.by : 0.f, hit ? 1 - L.bx - L.by : 0.f, L.hblas, L.htri};
+    L.st = S_EMPTY;
+    return;
+  }
   const f3 light_pos = mk3(a.light_pos.x, a.light_pos.y, a.light_pos.z);
   const f3 light_color = mk3(a.light_color.x, a.light_color.y, a.light_color.z);
   const f3 ambient = mk3(a.ambient_color.x, a.ambient_color.y, a.ambient_color.z);
@@ -369,7 +390,7 @@ __device__ __forceinline__ void post(Lane &L, const Smem &sm, const RenderA &p, 
 
 template <uint32_t MODE, bool STRICT, bool STATS>
 __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(const __grid_constant__ RenderA p) {
-  constexpr uint32_t kCols = (MODE & 1u) ? C_SHADOW_END : C_BASE_END;
+  constexpr uint32_t kCols = (MODE == kModeTrace) ? C_BASE_END : ((MODE & 1u) ? C_SHADOW_END : C_BASE_END);
   __shared__ float s_cols[kCols * kBlockThreads];
   uint32_t stk_e[kStackSize];
   float stk_d[kStackSize];
@@ -384,6 +405,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   const uint32_t nbands = nbands_total > f.rank ? (nbands_total - f.rank + f.world - 1) / f.world : 0;
   f.tiles_per_band = (f.band_rows / kTileH) * f.tcols;
   f.total = nbands * f.tiles_per_band * 32u;
+  if (MODE == kModeTrace) f.total = (uint32_t)((p.count + 31u) / 32u * 32u);
 
   Lane L;
   L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.blas = 0;
@@ -428,6 +450,12 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
       bool take = mine && my_rank < avail;
       if (take) {
         uint32_t item = chunk_next + my_rank;
+        if (MODE == kModeTrace) {
+          if (item < p.count) {
+            sm.u(C_PIX) = item;
+            begin_trace(L, sm, p, item, lc);
+          }
+        } else {
         uint32_t tile = item >> 5, in_tile = item & 31u;
         uint32_t band_local = tile / f.tiles_per_band, r = tile % f.tiles_per_band;
         uint32_t trow = r / f.tcols, tcol = r % f.tcols;
@@ -438,6 +466,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
           sm.u(C_PIX) = pix;
           sm.put3(C_COLX, mk3(0, 0, 0));
           begin_sample<MODE>(L, sm, p, pix, 0, lc);
+        }
         }
       }
       unsigned took = __ballot_sync(0xffffffffu, take);
@@ -472,6 +501,12 @@ int launch_mm(const RenderA &p, int num_sms, cudaStream_t stream) {
 }
 
 }  // namespace
+
+int launch_trace_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
+  if (p.count == 0) return 0;
+  if (p.strict_order) return p.stats ? launch_m<kModeTrace, true, true>(p, num_sms, stream) : launch_m<kModeTrace, true, false>(p, num_sms, stream);
+  return p.stats ? launch_m<kModeTrace, false, true>(p, num_sms, stream) : launch_m<kModeTrace, false, false>(p, num_sms, stream);
+}
 
 int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
   if (p.strict_order) return p.stats ? launch_mm<true, true>(p, num_sms, stream) : launch_mm<true, false>(p, num_sms, stream);

@@ -38,6 +38,10 @@ struct RenderA {
   uint32_t quorum_refill;   // ray state machine: run GEN/POST when fewer lanes than this are traversing
   uint32_t chunk;           //                    pixels a warp reserves per atomicAdd on the work counter
   uint32_t quorum_inner;    //                    leave the inner-node loop when fewer lanes than this hold an inner node
+  // hit-record mode of the state machine (launch_trace_machine): closest-hit records instead of pixels
+  const float *rays;        // 6 floats per ray, or nullptr => primary rays of `arg`
+  HitA *hits;
+  uint64_t count;
 };
 
 struct TraceA {
@@ -59,6 +63,8 @@ int launch_render_a(const RenderA &p, int num_sms, cudaStream_t stream);
 int launch_trace_a(const TraceA &p, int num_sms, cudaStream_t stream);
 // the warp-scheduled ray state machine (rt_machine.cu); scenes must have < 2^27 BVH nodes (else use launch_render_a)
 int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream);
+// same machine, work items = rays p.rays[0..count) (or primary rays), output = p.hits; count < 2^32
+int launch_trace_machine(const RenderA &p, int num_sms, cudaStream_t stream);
 constexpr uint64_t kMachineMaxNodes = 1ull << 27;
 
 }  // namespace vxb

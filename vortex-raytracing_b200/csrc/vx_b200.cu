@@ -466,10 +466,30 @@ private:
       bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes;
       rc = simple ? launch_render_a(p, prop_.multiProcessorCount, stream_) : launch_render_machine(p, prop_.multiProcessorCount, stream_);
     } else {
-      TraceA p{};
-      p.scene = sc, p.arg = a, p.rays = rays, p.count = count, p.hits = hits;
-      p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER), p.counters = counters_, p.stats = stats_on_;
-      rc = launch_trace_a(p, prop_.multiProcessorCount, stream_);
+      uint64_t bvh_bytes = 0;
+      const uint8_t *dummy = nullptr;
+      resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &dummy, &bvh_bytes);
+      bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes ||
+                    count >= 0xFFFFFFE0ull;
+      if (simple) {
+        TraceA p{};
+        p.scene = sc, p.arg = a, p.rays = rays, p.count = count, p.hits = hits;
+        p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER), p.counters = counters_, p.stats = stats_on_;
+        rc = launch_trace_a(p, prop_.multiProcessorCount, stream_);
+      } else {   // the warp-scheduled ray state machine with rays as work items
+        RenderA p{};
+        p.scene = sc, p.arg = a, p.out = nullptr, p.part = Partition{};
+        p.mode = 0, p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
+        p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
+        p.quorum_refill = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_REFILL", 12);
+        p.quorum_inner = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_INNER", 8);
+        p.chunk = (uint32_t)env_u64("VORTEX_B200_TRACE_CHUNK", 32);
+        if (p.chunk < 1 || p.chunk > 65536) p.chunk = 32;
+        if (p.quorum_refill < 2 || p.quorum_refill > 32) p.quorum_refill = 12;
+        if (p.quorum_inner < 1 || p.quorum_inner >= p.quorum_refill) p.quorum_inner = p.quorum_refill / 2;
+        p.rays = rays, p.hits = hits, p.count = count;
+        rc = launch_trace_machine(p, prop_.multiProcessorCount, stream_);
+      }
     }
     if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
     launches_ += rc;
