@@ -481,11 +481,11 @@ private:
         p.scene = sc, p.arg = a, p.out = nullptr, p.part = Partition{};
         p.mode = 0, p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
         p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
-        p.quorum_refill = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_REFILL", 12);
-        p.quorum_inner = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_INNER", 8);
-        p.chunk = (uint32_t)env_u64("VORTEX_B200_TRACE_CHUNK", 32);
-        if (p.chunk < 1 || p.chunk > 65536) p.chunk = 32;
-        if (p.quorum_refill < 2 || p.quorum_refill > 32) p.quorum_refill = 12;
+        p.quorum_refill = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_REFILL", 16);
+        p.quorum_inner = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_INNER", 12);
+        p.chunk = (uint32_t)env_u64("VORTEX_B200_TRACE_CHUNK", 64);   // sweep: profiles/r01_sweep_trace_quorum_chunk.txt
+        if (p.chunk < 1 || p.chunk > 65536) p.chunk = 64;
+        if (p.quorum_refill < 2 || p.quorum_refill > 32) p.quorum_refill = 16;
         if (p.quorum_inner < 1 || p.quorum_inner >= p.quorum_refill) p.quorum_inner = p.quorum_refill / 2;
         p.rays = rays, p.hits = hits, p.count = count;
         rc = launch_trace_machine(p, prop_.multiProcessorCount, stream_);
