@@ -501,6 +501,11 @@ def run_incoherent(args, wl, name):
     hbm, hbm_src, sm_mhz = peaks()
     achieved = abytes / (k_ms * 1e-3) / 1e9
     fp32_peak = tr.dev.caps(0x3) * 128 * 2 * sm_mhz * 1e6 / 1e12
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(name)
+    except Exception:
+        pass
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -533,7 +538,7 @@ def run_incoherent(args, wl, name):
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 24, "steps": e2e_steps,
                         "timer": "host wall clock around vx_copy_to_dev(rays) + vx_b200_trace_rays + vx_ready_wait + vx_copy_from_dev(hits), max over ranks"},
                 "gpu_launches": int(launches_per_step) * args.steps,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
                              "peak_source": hbm_src, "kernel": "k_render_m<trace> (ray state machine, rays as work items)", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes,
                              "algorithmic_bytes_per_ray": abytes / R,
                              "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
