@@ -52,6 +52,7 @@ struct Lane {
   uint32_t cur, sp, st;
   uint32_t blas;
   const uint8_t *nodes;   // first node of the instance being traversed
+  const uint8_t *wide;    // its 4-wide records (fast order), same node indexing
 };
 
 // cursor of a child node: small leaves and inner nodes carry (triCount, leftFirst) so the node is never re-read; payloads
@@ -130,6 +131,50 @@ __device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool caref
   }
 }
 
+// one visit of a 4-wide record (GpuNode4): the cursor's payload is the inner BVH2 node whose grandchildren are tested.
+// Nearest slot next, the others pushed farthest first; every pushed entry carries its entry distance for the re-cull at pop.
+template <bool STATS>
+__device__ __forceinline__ void step_wide(Lane &L, bool careful, uint32_t *stk_e, float *stk_d, Local &lc) {
+  const uint8_t *w = L.wide + (size_t)L.cur * sizeof(GpuNode4);
+  float4 lox = ldg4(w), loy = ldg4(w + 16), loz = ldg4(w + 32), hix = ldg4(w + 48), hiy = ldg4(w + 64), hiz = ldg4(w + 80);
+  uint4 ds = __ldg(reinterpret_cast<const uint4 *>(w + 96));
+  float d[4];
+  uint32_t e[4] = {ds.x, ds.y, ds.z, ds.w};
+  const float kInf = __int_as_float(0x7F800000);
+  {
+    float t;
+    bool h;
+    h = slab_hit(make_float4(lox.x, loy.x, loz.x, 0.f), make_float4(hix.x, hiy.x, hiz.x, 0.f), L.o, L.id, careful, L.dist, t);
+    d[0] = h ? t : kInf;
+    h = slab_hit(make_float4(lox.y, loy.y, loz.y, 0.f), make_float4(hix.y, hiy.y, hiz.y, 0.f), L.o, L.id, careful, L.dist, t);
+    d[1] = h ? t : kInf;
+    h = slab_hit(make_float4(lox.z, loy.z, loz.z, 0.f), make_float4(hix.z, hiy.z, hiz.z, 0.f), L.o, L.id, careful, L.dist, t);
+    d[2] = h ? t : kInf;
+    h = slab_hit(make_float4(lox.w, loy.w, loz.w, 0.f), make_float4(hix.w, hiy.w, hiz.w, 0.f), L.o, L.id, careful, L.dist, t);
+    d[3] = h ? t : kInf;   // unused slots hold NaN boxes: every comparison of the slab test fails
+  }
+  if (STATS) lc.box += 4;
+#define VXB_CSWAP(i, j)                       \
+  if (d[j] < d[i]) {                          \
+    float td = d[i]; d[i] = d[j]; d[j] = td;  \
+    uint32_t te = e[i]; e[i] = e[j]; e[j] = te; \
+  }
+  VXB_CSWAP(0, 1) VXB_CSWAP(2, 3) VXB_CSWAP(0, 2) VXB_CSWAP(1, 3) VXB_CSWAP(1, 2)
+#undef VXB_CSWAP
+  if (d[0] < kInf) {
+    if (L.sp + 3 <= kStackSize) {
+      if (d[3] < kInf) { stk_e[L.sp] = e[3]; stk_d[L.sp] = d[3]; ++L.sp; }
+      if (d[2] < kInf) { stk_e[L.sp] = e[2]; stk_d[L.sp] = d[2]; ++L.sp; }
+      if (d[1] < kInf) { stk_e[L.sp] = e[1]; stk_d[L.sp] = d[1]; ++L.sp; }
+    } else {
+      lc.err |= 1u;   // stack overflow: vx_ready_wait reports the run as failed
+    }
+    L.cur = e[0];
+  } else {
+    pop<false>(L, stk_e, stk_d);
+  }
+}
+
 // everything that is not an inner-node pair: leaves, nodes that must be read first, TLAS nodes / instance entry
 template <bool STRICT, bool STATS>
 __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA &sc, uint32_t *stk_e, float *stk_d, Local &lc) {
@@ -153,7 +198,9 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       L.d = od, L.o = oo;
       L.st |= F_INBLAS;
       set_recip(L);
-      L.nodes = sc.nodes + (size_t)__ldg(&blas->bvh_offset) * sizeof(BvhNodeA);
+      const size_t off = __ldg(&blas->bvh_offset);
+      L.nodes = sc.nodes + off * sizeof(BvhNodeA);
+      L.wide = reinterpret_cast<const uint8_t *>(sc.wide) + off * sizeof(GpuNode4);
       L.blas = bi;
       L.cur = kReadNode << kKindShift;   // node 0 of the instance
       if (STATS) lc.blas++;
@@ -197,8 +244,8 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
     }
     first = __float_as_uint(a.w);
     count = __float_as_uint(b.w);
-    if (count == 0) {   // an inner node after all: its child pair is visited by the inner loop
-      L.cur = first & kPay;
+    if (count == 0) {   // an inner node after all: visited by the inner loop (its child pair, or its 4-wide record)
+      L.cur = STRICT ? (first & kPay) : (L.cur & kPay);
       return;
     }
   }
@@ -236,7 +283,10 @@ __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &
       bool inner = is_inner(L);
       unsigned m = __ballot_sync(0xffffffffu, inner);
       if ((uint32_t)__popc(m) < inner_quorum) break;
-      if (inner) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);
+      if (inner) {
+        if (STRICT) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);   // the reference's own BVH2 walk
+        else step_wide<STATS>(L, careful, stk_e, stk_d, lc);                        // 4-wide records (the launch guarantees sc.wide)
+      }
     }
     if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
     unsigned t = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
@@ -408,7 +458,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   if (MODE == kModeTrace) f.total = (uint32_t)((p.count + 31u) / 32u * 32u);
 
   Lane L;
-  L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.blas = 0;
+  L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.wide = reinterpret_cast<const uint8_t *>(p.scene.wide), L.blas = 0;
   L.o = L.d = L.id = mk3(0, 0, 0);
   Local lc{0, 0, 0, 0, 0};
   uint32_t chunk_next = 0, chunk_end = 0;
@@ -504,11 +554,13 @@ int launch_mm(const RenderA &p, int num_sms, cudaStream_t stream) {
 
 int launch_trace_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
   if (p.count == 0) return 0;
+  if (!p.strict_order && !p.scene.wide) return -(int)cudaErrorInvalidValue;   // fast order walks the 4-wide records
   if (p.strict_order) return p.stats ? launch_m<kModeTrace, true, true>(p, num_sms, stream) : launch_m<kModeTrace, true, false>(p, num_sms, stream);
   return p.stats ? launch_m<kModeTrace, false, true>(p, num_sms, stream) : launch_m<kModeTrace, false, false>(p, num_sms, stream);
 }
 
 int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
+  if (!p.strict_order && !p.scene.wide) return -(int)cudaErrorInvalidValue;   // fast order walks the 4-wide records
   if (p.strict_order) return p.stats ? launch_mm<true, true>(p, num_sms, stream) : launch_mm<true, false>(p, num_sms, stream);
   return p.stats ? launch_mm<false, true>(p, num_sms, stream) : launch_mm<false, false>(p, num_sms, stream);
 }

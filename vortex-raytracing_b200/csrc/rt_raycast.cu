@@ -374,6 +374,57 @@ __global__ void k_gather_tris(const float *__restrict__ tri, const uint32_t *__r
   gtri[p] = g;
 }
 
+// ---- BVH2 -> 4-wide records (see GpuNode4) ----
+__device__ __forceinline__ uint32_t wide_desc(uint32_t leftFirst, uint32_t triCount, uint32_t nodeIdx) {
+  if (triCount == 0) return nodeIdx;                                   // inner: kind 0, payload = its own (instance-local) index
+  if (triCount < 15u && leftFirst < (1u << 27)) return (triCount << 27) | leftFirst;
+  return (15u << 27) | nodeIdx;                                        // big leaf: read the node when visited
+}
+__global__ void k_build_wide(const uint8_t *__restrict__ nodes, uint64_t n_nodes, const uint32_t *__restrict__ bases, uint32_t n_bases,
+                             GpuNode4 *__restrict__ wide) {
+  uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_nodes) return;
+  const uint8_t *n = nodes + g * sizeof(BvhNodeA);
+  float4 a = ldg4(n), b = ldg4(n + 16);
+  if (__float_as_uint(b.w) != 0) return;                               // a leaf has no wide record
+  // instance base: last entry of `bases` that is <= g
+  uint32_t lo = 0, hi = n_bases;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) / 2;
+    if (bases[mid] <= g) lo = mid;
+    else hi = mid;
+  }
+  const uint64_t base = n_bases ? bases[lo] : 0;
+  const uint64_t end = (lo + 1 < n_bases) ? bases[lo + 1] : n_nodes;
+  GpuNode4 w;
+  const float qnan = __uint_as_float(0x7FC00000u);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    w.lox[k] = w.loy[k] = w.loz[k] = w.hix[k] = w.hiy[k] = w.hiz[k] = qnan;
+    w.desc[k] = 0xFFFFFFFFu;
+    w._pad[k] = 0;
+  }
+  int slot = 0;
+  auto put = [&](uint32_t local) {                                       // child `local` (instance-local index) becomes a slot
+    const uint8_t *c = nodes + (base + local) * sizeof(BvhNodeA);
+    float4 c0 = ldg4(c), c1 = ldg4(c + 16);
+    w.lox[slot] = c0.x, w.loy[slot] = c0.y, w.loz[slot] = c0.z;
+    w.hix[slot] = c1.x, w.hiy[slot] = c1.y, w.hiz[slot] = c1.z;
+    w.desc[slot] = wide_desc(__float_as_uint(c0.w), __float_as_uint(c1.w), local);
+    ++slot;
+  };
+  const uint32_t first = __float_as_uint(a.w);
+  for (uint32_t c = first; c < first + 2; ++c) {
+    if (base + c + 0 >= end) continue;                                  // malformed index: leave the slot unused
+    const uint8_t *cn = nodes + (base + c) * sizeof(BvhNodeA);
+    float4 c0 = ldg4(cn), c1 = ldg4(cn + 16);
+    uint32_t cfirst = __float_as_uint(c0.w), ccount = __float_as_uint(c1.w);
+    if (ccount != 0 || base + cfirst + 1 >= end) put(c);                 // leaf child (or malformed grandchildren): one slot
+    else put(cfirst), put(cfirst + 1);                                   // inner child: its two children
+  }
+  wide[g] = w;
+}
+
 template <uint32_t MODE, bool STRICT, bool STATS>
 int launch_render_t(const RenderA &p, int num_sms, cudaStream_t stream) {
   auto kern = k_render_a<MODE, STRICT, STATS>;
@@ -403,6 +454,13 @@ cudaError_t launch_gather_tris(const TriA *tri, const uint32_t *triIdx, GpuTri *
   if (n_slots == 0) return cudaSuccess;
   unsigned blocks = (unsigned)((n_slots + 255) / 256);
   k_gather_tris<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float *>(tri), triIdx, gtri, n_slots, n_tris);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_build_wide(const uint8_t *nodes, uint64_t n_nodes, const uint32_t *bases, uint32_t n_bases, GpuNode4 *wide,
+                              cudaStream_t stream) {
+  if (n_nodes == 0) return cudaSuccess;
+  k_build_wide<<<(unsigned)((n_nodes + 127) / 128), 128, 0, stream>>>(nodes, n_nodes, bases, n_bases, wide);
   return cudaGetLastError();
 }
 

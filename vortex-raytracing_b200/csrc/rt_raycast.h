@@ -5,10 +5,24 @@
 
 namespace vxb {
 
+// GPU-side 4-wide node derived from the uploaded BVH2 (fast order only; strict order walks the BVH2 in place): wide[n] holds,
+// for the inner BVH2 node n of an instance, the boxes of its grandchildren (a child that is a leaf stays one slot) — the very
+// float boxes of the uploaded bvh_node_t records, SoA, plus one descriptor per slot.  One 128-byte line per visit, half as
+// many visits, pops and dependent loads per ray as the 2-wide walk; same closest hit (a superset/subset of the same exact
+// box tests never changes the minimum-t triangle, only which of several equal-t triangles is met first).
+struct alignas(128) GpuNode4 {
+  float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];   // NaN boxes in unused slots
+  uint32_t desc[4];     // slot cursor: kind<<27 | payload (rt_machine.cu: 0 = inner node index, 1..14 = leaf with that many
+                        // triangles at payload, 15 = read node payload); 0xFFFFFFFF = unused slot
+  uint32_t _pad[4];
+};
+static_assert(sizeof(GpuNode4) == 128, "GpuNode4");
+
 // Device pointers of one uploaded layout-A scene (already translated from Vortex addresses).
 struct SceneA {
   const uint8_t *nodes;     // BvhNodeA[]  — consumed in place (a node pair is one 64-byte, 32-byte-aligned record)
   const GpuTri *gtri;       // one per triIdx slot (built by launch_gather_tris)
+  const GpuNode4 *wide;     // one per bvh_node_t slot (built by launch_build_wide), or nullptr
   const TlasNodeA *tlas;
   const BlasNodeA *blas;
   const TriExA *triEx;
@@ -58,6 +72,10 @@ struct TraceA {
 // gtri[p] = triangle triIdx[p] in edge form, p in [0, n_slots).  Slots whose index is >= n_tris get a degenerate triangle.
 cudaError_t launch_gather_tris(const TriA *tri, const uint32_t *triIdx, GpuTri *gtri, uint64_t n_slots, uint64_t n_tris,
                                cudaStream_t stream);
+// wide[g] for every inner node g in [0, n_nodes); bases = ascending bvh_offset values of the instances (child indices are
+// instance-local: node g belongs to the last base <= g)
+cudaError_t launch_build_wide(const uint8_t *nodes, uint64_t n_nodes, const uint32_t *bases, uint32_t n_bases, GpuNode4 *wide,
+                              cudaStream_t stream);
 // returns the number of kernels launched (>0) or a negative cudaError_t
 int launch_render_a(const RenderA &p, int num_sms, cudaStream_t stream);
 int launch_trace_a(const TraceA &p, int num_sms, cudaStream_t stream);

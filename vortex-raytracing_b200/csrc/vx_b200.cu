@@ -23,6 +23,7 @@
 #include "address_space.h"
 #include "rt_raycast.h"
 #include "rt_rtu.h"
+#include <algorithm>
 
 #define VXB_EXPORT extern "C" __attribute__((visibility("default")))
 
@@ -103,6 +104,9 @@ public:
     if (remote_base_) cudaIpcCloseMemHandle(remote_base_);
     remote_base_ = nullptr, remote_fb_ = nullptr;
     if (gtri_) cudaFree(gtri_);
+    if (wide_) cudaFree(wide_);
+    if (wide_bases_) cudaFree(wide_bases_);
+    wide_ = nullptr, wide_bases_ = nullptr, wide_valid_ = false;
     if (rtu_nodes_) cudaFree(rtu_nodes_);
     if (rtu_tri_) cudaFree(rtu_tri_);
     if (counters_) cudaFree(counters_);
@@ -446,8 +450,55 @@ private:
       gtri_slots_ = n_slots;
       ++launches_, ++prep_launches_;
     }
-    CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     sc.gtri = gtri_;
+    sc.wide = nullptr;
+    {   // 4-wide records for the state machine's fast order, cached on (bvh, blas) addresses + upload generations
+      uint64_t bvh_bytes = 0, bvh_gen = 0, blas_bytes = 0, blas_gen = 0;
+      const uint8_t *nodes = nullptr, *blas_raw = nullptr;
+      resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &nodes, &bvh_bytes, &bvh_gen);
+      resolve(a.blas_addr, sizeof(BlasNodeA), 8, "blas", &blas_raw, &blas_bytes, &blas_gen);
+      const uint64_t n_nodes = bvh_bytes / sizeof(BvhNodeA), n_blas = blas_bytes / sizeof(BlasNodeA);
+      const bool machine = dcr_get(VX_DCR_B200_RT_KERNEL) != 1 && n_nodes < kMachineMaxNodes && n_slots < kMachineMaxNodes;
+      const bool want = machine && dcr_get(VX_DCR_B200_RT_ORDER) == 0 && n_nodes > 0 && n_blas > 0;
+      if (want) {
+        uint64_t key[5] = {a.bvh_addr, a.blas_addr, bvh_gen, blas_gen, n_nodes};
+        if (!wide_valid_ || memcmp(key, wide_key_, sizeof(key)) != 0) {
+          // instance bases: the bvh_offset field of every blas_node_t (child indices are instance-local)
+          std::vector<uint8_t> hb(n_blas * sizeof(BlasNodeA));
+          CUDA_TRY(cudaMemcpyAsync(hb.data(), blas_raw, hb.size(), cudaMemcpyDeviceToHost, stream_));
+          CUDA_TRY(cudaStreamSynchronize(stream_));
+          std::vector<uint32_t> bases;
+          for (uint64_t i = 0; i < n_blas; ++i) {
+            uint32_t off;
+            memcpy(&off, hb.data() + i * sizeof(BlasNodeA) + offsetof(BlasNodeA, bvh_offset), 4);
+            if (off < n_nodes) bases.push_back(off);
+          }
+          std::sort(bases.begin(), bases.end());
+          bases.erase(std::unique(bases.begin(), bases.end()), bases.end());
+          if (bases.empty() || bases[0] != 0) bases.insert(bases.begin(), 0u);
+          if (wide_cap_ < n_nodes) {
+            if (wide_) cudaFree(wide_);
+            wide_ = nullptr, wide_cap_ = 0;
+            CUDA_TRY(cudaMalloc(&wide_, n_nodes * sizeof(GpuNode4)));
+            wide_cap_ = n_nodes;
+          }
+          if (wide_bases_cap_ < bases.size()) {
+            if (wide_bases_) cudaFree(wide_bases_);
+            wide_bases_ = nullptr, wide_bases_cap_ = 0;
+            CUDA_TRY(cudaMalloc(&wide_bases_, bases.size() * 4));
+            wide_bases_cap_ = bases.size();
+          }
+          CUDA_TRY(cudaMemcpyAsync(wide_bases_, bases.data(), bases.size() * 4, cudaMemcpyHostToDevice, stream_));
+          CUDA_TRY(cudaStreamSynchronize(stream_));   // `bases` is a local
+          CUDA_TRY(launch_build_wide(nodes, n_nodes, wide_bases_, (uint32_t)bases.size(), wide_, stream_));
+          memcpy(wide_key_, key, sizeof(key));
+          wide_valid_ = true;
+          ++launches_, ++prep_launches_;
+        }
+        sc.wide = wide_;
+      }
+    }
+    CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     int rc;
     if (!trace) {
       RenderA p{};
@@ -463,14 +514,15 @@ private:
       uint64_t bvh_bytes = 0;
       const uint8_t *dummy = nullptr;
       resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &dummy, &bvh_bytes);
-      bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes;
+      bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes ||
+                    (dcr_get(VX_DCR_B200_RT_ORDER) == 0 && !sc.wide);
       rc = simple ? launch_render_a(p, prop_.multiProcessorCount, stream_) : launch_render_machine(p, prop_.multiProcessorCount, stream_);
     } else {
       uint64_t bvh_bytes = 0;
       const uint8_t *dummy = nullptr;
       resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &dummy, &bvh_bytes);
       bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes ||
-                    count >= 0xFFFFFFE0ull;
+                    count >= 0xFFFFFFE0ull || (dcr_get(VX_DCR_B200_RT_ORDER) == 0 && !sc.wide);
       if (simple) {
         TraceA p{};
         p.scene = sc, p.arg = a, p.rays = rays, p.count = count, p.hits = hits;
@@ -610,6 +662,11 @@ private:
   GpuTri *gtri_ = nullptr;
   uint64_t gtri_cap_ = 0, gtri_slots_ = 0;
   uint64_t gtri_key_[4] = {0, 0, 0, 0};
+  // layout-A 4-wide records (fast order of the state machine)
+  GpuNode4 *wide_ = nullptr;
+  uint32_t *wide_bases_ = nullptr;
+  uint64_t wide_cap_ = 0, wide_bases_cap_ = 0, wide_key_[5] = {0};
+  bool wide_valid_ = false;
   // layout-B decoded nodes (TLAS then BLAS) and edge-form triangles
   GpuNodeB *rtu_nodes_ = nullptr;
   GpuTri *rtu_tri_ = nullptr;
