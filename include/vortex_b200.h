@@ -188,6 +188,16 @@ int vx_b200_get_stats(vx_device_h hdevice, vx_b200_stats_t *stats);
 int vx_b200_trace_primary(vx_device_h hdevice, vx_buffer_h harguments, vx_buffer_h hhits);
 int vx_b200_trace_rays(vx_device_h hdevice, vx_buffer_h harguments, vx_buffer_h hrays, uint64_t count, vx_buffer_h hhits);
 
+/* GPU BVH build: builds the layout-A BVH2 of `tri_count` triangles that already sit in `htri` (tri_t records
+ * starting at triangle index tri_first) into `hbvh` (bvh_node_t records from node index node_first; 2*tri_count-1 are written)
+ * and `htriIdx` (uint32 slots from slot_first; values are GLOBAL triangle indices tri_first+i in leaf order) — the byte layouts
+ * of tests/regression/raycast/common.h:32-44 and scene.cpp:51, i.e. what BVH::build (raycast/bvh.cpp:23-66) leaves in those
+ * buffers, so a host can point blas_node_t.bvh_offset at node_first and proceed exactly as after its own CPU build (or
+ * download the buffers and hand them to any other Vortex backend).  Linear BVH (Morton sort + Karras radix tree), exact
+ * vertex min/max boxes, one-triangle leaves.  Synchronous.  *nodes_used receives 2*tri_count-1. */
+int vx_b200_build_bvh(vx_device_h hdevice, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h hbvh,
+                      uint64_t node_first, vx_buffer_h htriIdx, uint64_t slot_first, uint64_t *nodes_used);
+
 /* Human-readable description of the last error on this thread ("" if none). */
 const char *vx_b200_last_error(void);
 

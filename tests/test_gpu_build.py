@@ -1,0 +1,88 @@
+"""GPU BVH build (vx_b200_build_bvh): the tree it leaves in the Vortex buffers is the reference's layout-A byte
+format, so the checks run the REFERENCE's own traversal (CPU oracle, RawScene) on the downloaded buffers:
+  * structure: 2N-1 nodes, children adjacent, every triangle in exactly one leaf, boxes contain their subtree;
+  * the oracle on the GPU-built tree finds the same closest-hit distances as on the host-built (reference-identical) tree;
+  * the CUDA kernels on the GPU-built tree equal the oracle on the same bytes (strict order bit for bit)."""
+import numpy as np
+import pytest
+
+from rt_common import assert_hit_gates, best_oracle, hit_parity, pyoracle, scenes, tracer_mod, vx
+
+pytestmark = pytest.mark.gpu
+po = pyoracle()
+BVH_DT = np.dtype([("lo", "<f4", 3), ("leftFirst", "<u4"), ("hi", "<f4", 3), ("triCount", "<u4")])
+
+
+def gpu_built_scene(oracle, mesh, w, h):
+    sc = oracle.scene_create([mesh])
+    karg = sc.setup(w, h)
+    bufs = sc.buffers()
+    n = mesh["tris"].shape[0]
+    tr = tracer_mod.Tracer(w, h, 1, 1).init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names})
+    used = tr.dev.build_bvh(tr.bufs["tri"], n, tr.bufs["bvh"], tr.bufs["triIdx"])
+    assert used == 2 * n - 1
+    st = tr.dev.stats()
+    bvh = np.zeros(len(bufs["bvh"]), np.uint8)
+    idx = np.zeros(len(bufs["triIdx"]), np.uint8)
+    tr.bufs["bvh"].copy_from_dev(bvh)
+    tr.bufs["triIdx"].copy_from_dev(idx)
+    gb = dict(bufs)
+    gb["bvh"], gb["triIdx"] = bvh, idx
+    # TLAS leaf box = the root box, which any correct build reproduces exactly
+    nodes = bvh.view(BVH_DT)
+    host_root = bufs["bvh"].view(BVH_DT)[0]
+    assert np.array_equal(nodes[0]["lo"], host_root["lo"]) and np.array_equal(nodes[0]["hi"], host_root["hi"])
+    return sc, karg, bufs, gb, tr, st
+
+
+@pytest.mark.parametrize("name,mk", [("cornell", lambda: scenes.cornell_box()), ("hf64", lambda: scenes.heightfield(64)),
+                                     ("ico3", lambda: scenes.icosphere((0, 0, 0), 1.0, 3))], ids=["cornell", "hf64", "ico3"])
+def test_gpu_built_bvh(name, mk):
+    oracle = best_oracle()
+    mesh = mk()
+    n = mesh["tris"].shape[0]
+    sc, karg, bufs, gb, tr, st = gpu_built_scene(oracle, mesh, 96, 72)
+    try:
+        nodes = gb["bvh"].view(BVH_DT)[: 2 * n - 1]
+        idx = gb["triIdx"].view(np.uint32)
+        assert sorted(idx.tolist()) == list(range(n))
+        leaves = nodes[nodes["triCount"] != 0]
+        assert len(leaves) == n and (leaves["triCount"] == 1).all() and sorted(leaves["leftFirst"].tolist()) == list(range(n))
+        inner = np.flatnonzero(nodes["triCount"] == 0)
+        assert len(inner) == n - 1
+        # boxes: a parent's box is the union of its two (adjacent) children; a leaf's box is its triangle's vertex min/max
+        l, r = nodes[nodes["leftFirst"][inner]], nodes[nodes["leftFirst"][inner] + 1]
+        assert np.array_equal(nodes["lo"][inner], np.minimum(l["lo"], r["lo"])) and np.array_equal(nodes["hi"][inner], np.maximum(l["hi"], r["hi"]))
+        tri = bufs["tri"].view(np.float32).reshape(-1, 3, 3)[idx[leaves["leftFirst"]]]
+        assert np.array_equal(leaves["lo"], tri.min(axis=1)) and np.array_equal(leaves["hi"], tri.max(axis=1))
+        # the reference's traversal on the GPU-built tree vs on the host-built tree
+        raw = po.RawScene(oracle, gb, karg)
+        h_gpu_tree = raw.trace_primary(threads=oracle.hw_threads())
+        h_host_tree = sc.trace_primary(threads=oracle.hw_threads())
+        assert np.array_equal(h_gpu_tree["dist"], h_host_tree["dist"])
+        assert_hit_gates(hit_parity(h_gpu_tree, h_host_tree), False)
+        # the CUDA kernels on the GPU-built tree vs the oracle on the same bytes
+        for strict in (1, 0):
+            tr.set_mode(0, strict)
+            assert_hit_gates(hit_parity(tr.trace_primary(), h_gpu_tree), strict)
+        img = tr.run()
+        ref_img, _ = raw.render(threads=oracle.hw_threads())
+        assert np.abs(((img >> 8) & 255).astype(int) - ((ref_img >> 8) & 255).astype(int)).max() <= 1
+        assert st["kernel_launches"] >= 5
+    finally:
+        tr.close()
+
+
+def test_gpu_build_one_triangle_and_errors():
+    one = scenes.heightfield(1)
+    mesh = {"tris": one["tris"][:1], "triex": one["triex"][:1], "tex": one["tex"], "reflectivity": 0.0}
+    oracle = best_oracle()
+    sc, karg, bufs, gb, tr, st = gpu_built_scene(oracle, mesh, 8, 8)
+    try:
+        root = gb["bvh"].view(BVH_DT)[0]
+        assert root["triCount"] == 1 and root["leftFirst"] == 0
+        with pytest.raises(vx.VxError):
+            tr.dev.build_bvh(tr.bufs["tri"], 5, tr.bufs["bvh"], tr.bufs["triIdx"])   # more triangles than the buffer holds
+    finally:
+        tr.close()

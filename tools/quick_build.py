@@ -1,0 +1,43 @@
+"""GPU vs host BVH build time and the tracing cost of the resulting trees (scratch tool): python tools/quick_build.py [n]"""
+import importlib
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+scenes = importlib.import_module("vortex-raytracing_b200.scenes")
+host = importlib.import_module("vortex-raytracing_b200.host")
+tracer_mod = importlib.import_module("vortex-raytracing_b200.tracer")
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 708
+w, h = 3840, 2160
+mesh = scenes.heightfield(n)
+t0 = time.perf_counter()
+hs = host.HostScene([mesh])
+karg = hs.setup(w, h)
+bufs = hs.buffers()
+host_s = time.perf_counter() - t0
+tr = tracer_mod.Tracer(w, h, 1, 1).init(bufs)
+tr.setup({k: karg[k][0] for k in karg.dtype.names})
+tr.set_mode(0, 0)
+tr._upload_args()
+
+
+def frame_ms():
+    ms = []
+    for i in range(6):
+        tr.launch()
+        if i >= 2:
+            ms.append(tr.dev.last_kernel_ms())
+    return float(np.mean(ms))
+
+
+host_ms = frame_ms()
+nt = mesh["tris"].shape[0]
+tr.dev.build_bvh(tr.bufs["tri"], nt, tr.bufs["bvh"], tr.bufs["triIdx"])
+tr.dev.build_bvh(tr.bufs["tri"], nt, tr.bufs["bvh"], tr.bufs["triIdx"])
+gpu_build_ms = tr.dev.stats()["kernel_ms"]
+gpu_ms = frame_ms()
+print(f"triangles={nt} host_build_s={host_s:.3f} gpu_build_ms={gpu_build_ms:.2f} primary_4k_frame_ms host_tree={host_ms:.3f} gpu_tree={gpu_ms:.3f}")
+tr.close()

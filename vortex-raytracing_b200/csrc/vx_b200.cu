@@ -23,6 +23,7 @@
 #include "address_space.h"
 #include "rt_raycast.h"
 #include "rt_rtu.h"
+#include "rt_build.h"
 #include <algorithm>
 
 #define VXB_EXPORT extern "C" __attribute__((visibility("default")))
@@ -295,6 +296,40 @@ public:
     if (world == 0 || rank >= world) return fail("bad partition rank=%u world=%u", rank, world);
     if (band_rows == 0 || band_rows % 4 != 0) return fail("band_rows must be a positive multiple of 4");
     part_.rank = rank, part_.world = world, part_.band_rows = band_rows;
+    return 0;
+  }
+  int build_bvh(uint64_t tri_addr, uint64_t tri_count, uint64_t tri_first, uint64_t bvh_addr, uint64_t idx_addr, uint64_t *nodes_used) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    if (tri_count == 0 || tri_count > 0x7FFFFFFFull) return fail("vx_b200_build_bvh: bad triangle count");
+    if (run_pending_) {
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+    }
+    const TriA *tri = nullptr;
+    BvhNodeA *nodes = nullptr;
+    uint32_t *idx = nullptr;
+    if (resolve(tri_addr, tri_count * sizeof(TriA), 4, "tri", &tri)) return -1;
+    if (resolve(bvh_addr, (2 * tri_count - 1) * sizeof(BvhNodeA), 16, "bvh", &nodes)) return -1;
+    if (resolve(idx_addr, tri_count * 4, 4, "triIdx", &idx)) return -1;
+    int nl = 0;
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, stream_));
+    int rc = build_lbvh(tri, (uint32_t)tri_count, nodes, idx, (uint32_t)tri_first, stream_, &nl);
+    cudaEventRecord(e1, stream_);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0), cudaEventDestroy(e1);
+    if (rc != 0) return fail("vx_b200_build_bvh: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    // the buffers changed under the caches keyed on upload generations
+    uint64_t start = 0;
+    if (auto *b = space_.find(bvh_addr, 1, &start)) b->write_gen = ++generation_;
+    if (auto *b = space_.find(idx_addr, 1, &start)) b->write_gen = ++generation_;
+    stats_.kernel_launches = (uint64_t)nl, stats_.prep_launches = 0, stats_.kernel_ms = ms, stats_.prep_ms = 0;
+    if (nodes_used) *nodes_used = 2 * tri_count - 1;
     return 0;
   }
   int set_remote_framebuffer(const void *handle, uint64_t offset, uint64_t bytes) {
@@ -927,6 +962,16 @@ VXB_EXPORT int vx_b200_select_device(int cuda_device) {
 VXB_EXPORT int vx_b200_set_partition(vx_device_h h, uint32_t rank, uint32_t world, uint32_t band_rows) {
   if (!h) return -1;
   return ((Device *)h)->set_partition(rank, world, band_rows);
+}
+VXB_EXPORT int vx_b200_build_bvh(vx_device_h h, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h hbvh,
+                                 uint64_t node_first, vx_buffer_h htriIdx, uint64_t slot_first, uint64_t *nodes_used) {
+  if (!h || !htri || !hbvh || !htriIdx) return -1;
+  auto t = (Buffer *)htri, b = (Buffer *)hbvh, i = (Buffer *)htriIdx;
+  if ((tri_first + tri_count) * sizeof(vxb::TriA) > t->size || (node_first + 2 * tri_count - 1) * sizeof(vxb::BvhNodeA) > b->size ||
+      (slot_first + tri_count) * 4 > i->size)
+    return fail("vx_b200_build_bvh: range outside a buffer");
+  return ((Device *)h)->build_bvh(t->addr + tri_first * sizeof(vxb::TriA), tri_count, tri_first, b->addr + node_first * sizeof(vxb::BvhNodeA),
+                                  i->addr + slot_first * 4, nodes_used);
 }
 VXB_EXPORT int vx_b200_export_buffer(vx_buffer_h hbuffer, void *ipc_handle_64, uint64_t *offset) {
   if (!hbuffer || !ipc_handle_64 || !offset) return -1;

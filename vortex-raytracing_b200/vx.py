@@ -64,6 +64,7 @@ def lib():
             "vx_b200_stream": [H, C.POINTER(u64)], "vx_b200_last_kernel_ms": [H, C.POINTER(C.c_float)],
             "vx_b200_enable_stats": [H, i32], "vx_b200_get_stats": [H, C.POINTER(Stats)],
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
+            "vx_b200_build_bvh": [H, B, u64, u64, B, u64, B, u64, C.POINTER(u64)],
             "vx_b200_export_buffer": [B, vp, C.POINTER(u64)], "vx_b200_set_remote_framebuffer": [H, vp, u64, u64],
         }
         for name, args in sig.items():
@@ -205,6 +206,14 @@ class Device:
         return v.value
 
     # ---- b200 extensions ----
+    def build_bvh(self, tri, tri_count, bvh, tri_idx, tri_first=0, node_first=0, slot_first=0):
+        """GPU build of the layout-A BVH2 of triangles [tri_first, tri_first+tri_count) of buffer `tri` into `bvh` / `tri_idx`;
+        returns the number of nodes written (2*tri_count-1)."""
+        used = C.c_uint64()
+        _check(lib().vx_b200_build_bvh(self.h, tri.h, tri_first, tri_count, bvh.h, node_first, tri_idx.h, slot_first, C.byref(used)),
+               "vx_b200_build_bvh")
+        return used.value
+
     def set_remote_framebuffer(self, handle, offset=0, nbytes=0):
         """handle: the 64 bytes of Buffer.ipc_export() from the image owner's process (None detaches)"""
         hb = C.create_string_buffer(bytes(handle), 64) if handle is not None else None
