@@ -24,7 +24,7 @@ EXPORTS = (
     "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
-    "vx_b200_select_device vx_b200_set_partition vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
     "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_last_error"
 ).split()
 
