@@ -103,6 +103,16 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def rt_unit_perf(st, order):
+    """RT-unit style counters of one run (SURVEY 8f-4; the shape of RTUnit::PerfStats, sim/simx/rt_unit.h:15-45) in traversal
+    steps instead of simulated cycles: a step = one node fetch + its box tests, or one leaf."""
+    if not st.get("warp_steps"):
+        return None
+    return {"order": order, "warps": st["warps"], "warp_steps": st["warp_steps"], "thread_steps": st["lane_steps"],
+            "simt_efficiency": st["lane_steps"] / (32.0 * st["warp_steps"]),
+            "thread_steps_per_ray": st["lane_steps"] / max(1, st["rays"])}
+
+
 def algorithmic_work(st, pixels):
     """bytes and flops of the REFERENCE algorithm for the counted work (layout A)."""
     b = 32 * st["box_tests"] + 40 * st["tri_tests"] + 160 * st["blas_entered"] + (60 + 160 + 4) * st["shaded_hits"] + 4 * pixels
@@ -329,8 +339,10 @@ def run_b200(args, wl, name):
     tr._upload_args()
     tr.launch()
     work = tr.dev.stats()
-    tr.dev.enable_stats(False)
     tr.set_mode(wl["mode"], 0)
+    tr.launch()
+    unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(work, "strict")]
+    tr.dev.enable_stats(False)
     pixels_rank = len(mg.owned_rows(rank, world, H, BAND_ROWS)) * W
     abytes, aflops = algorithmic_work(work, pixels_rank)
     k_ms = float(np.mean(kernel_ms))
@@ -379,7 +391,7 @@ def run_b200(args, wl, name):
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                         "timer": "host wall clock around the synchronous vx_* calls, max over ranks", "launches_per_step": e2e_launches},
-                "gpu_launches": int(launches_per_step) * args.steps,
+                "gpu_launches": int(launches_per_step) * args.steps, "rt_unit_perf": unit_perf,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
                              "peak_source": hbm_src, "kernel": "k_render_a" if args.kernel == 1 else "k_render_m", "kernel_ms": k_ms,
                              "algorithmic_bytes_per_launch": abytes, "algorithmic_bytes_per_ray": abytes / max(1, work["rays"]),
@@ -493,8 +505,11 @@ def run_incoherent(args, wl, name):
     tr.dev.trace_rays(tr.args, rb, R, hb)
     tr.dev.ready_wait()
     work = tr.dev.stats()
-    tr.dev.enable_stats(False)
     tr.set_mode(0, 0)
+    tr.dev.trace_rays(tr.args, rb, R, hb)
+    tr.dev.ready_wait()
+    unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(work, "strict")]
+    tr.dev.enable_stats(False)
     abytes = 32 * work["box_tests"] + 40 * work["tri_tests"] + 160 * work["blas_entered"] + 48 * R    # + ray in (24 B) and hit record out (24 B)
     aflops = 27 * work["box_tests"] + 53 * work["tri_tests"] + 30 * work["blas_entered"]
     k_ms = float(np.mean(kernel_ms))
@@ -537,7 +552,7 @@ def run_incoherent(args, wl, name):
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 24, "steps": e2e_steps,
                         "timer": "host wall clock around vx_copy_to_dev(rays) + vx_b200_trace_rays + vx_ready_wait + vx_copy_from_dev(hits), max over ranks"},
-                "gpu_launches": int(launches_per_step) * args.steps,
+                "gpu_launches": int(launches_per_step) * args.steps, "rt_unit_perf": unit_perf,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
                              "peak_source": hbm_src, "kernel": "k_render_m<trace> (ray state machine, rays as work items)", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes,
                              "algorithmic_bytes_per_ray": abytes / R,
@@ -608,6 +623,9 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
     tr.launch()
     wk = tr.dev.stats()
     strict_ms = tr.dev.last_kernel_ms()
+    tr.set_order(0)
+    tr.launch()
+    unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(wk, "strict")]
     tr.close()
     abytes = 52 * wk["box_tests"] + 52 * wk["blas_entered"] + 36 * wk["tri_tests"] + 156 * wk["shaded_hits"] + 4 * w * h
     k_ms = float(np.mean(ms))
@@ -617,6 +635,7 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
            "algorithmic_bytes_per_ray": abytes / max(1, rays), "roofline_hbm_frac": abytes / (k_ms * 1e-3) / 1e9 / hbm,
            "work_per_ray": {"nodes": wk["box_tests"] / max(1, rays), "tri_tests": wk["tri_tests"] / max(1, rays),
                             "blas_entered": wk["blas_entered"] / max(1, rays), "shaded_hits": wk["shaded_hits"] / max(1, rays)},
+           "rt_unit_perf": unit_perf,
            "note": "kernel time only, L2 not flushed; algorithmic work = the reference's trail/short-stack order (strict)"}
     if with_cpu:
         R = importlib.import_module("oracle.pyoracle_rtu")

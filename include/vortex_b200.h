@@ -172,6 +172,12 @@ typedef struct {
   uint64_t prep_launches;   /* of those: scene re-flatten kernels (0 when the cached GPU layout was reused) */
   float kernel_ms;          /* == vx_b200_last_kernel_ms */
   float prep_ms;            /* device time of the re-flatten pass inside the last run */
+  /* RT-unit style counters (the shape of RTUnit::PerfStats, sim/simx/rt_unit.h:15-45), statistics mode only:
+   * one step = one traversal iteration (node fetch + box tests, or one leaf); SIMT efficiency of the run =
+   * lane_steps / (32 * warp_steps), the figure simx prints as rt_total_simt_efficiency / rt_total_warps. */
+  uint64_t lane_steps;      /* traversal iterations summed over lanes   (~ rt_total_thread_latency) */
+  uint64_t warp_steps;      /* traversal iterations issued by warps      (~ rt_total_warp_latency) */
+  uint64_t warps;           /* warps that ran                            (~ rt_total_warps) */
 } vx_b200_stats_t;
 
 /* Statistics of the last completed run.  Work counters other than `rays` are gathered only after

@@ -163,6 +163,13 @@ def test_stats_match_oracle_counters():
         st = tr.dev.stats()
         for k in ("rays", "box_tests", "tri_tests", "blas_entered", "shaded_hits"):
             assert st[k] == cnt[k], (k, st[k], cnt[k])
+        # RT-unit style counters (RTUnit::PerfStats): SIMT efficiency of the run is a fraction, and without statistics they are 0
+        eff = st["lane_steps"] / (32.0 * st["warp_steps"])
+        assert st["warps"] > 0 and 0.0 < eff <= 1.0
+        tr.dev.enable_stats(False)
+        tr.run()
+        st = tr.dev.stats()
+        assert st["rays"] == cnt["rays"] and st["warp_steps"] == 0 and st["lane_steps"] == 0
     finally:
         tr.close()
 

@@ -59,6 +59,9 @@ def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
                 assert hits.tobytes() == hits_port.tobytes()
                 # work counters of the reference algorithm: node reads, instance entries, triangle tests
                 assert (st["box_tests"], st["blas_entered"], st["tri_tests"]) == (work["nodes"], work["blas_entered"], work["tri_tests"]), (st, work)
+                # RT-unit style counters: one traversal step per node the reference reads
+                assert st["lane_steps"] == work["nodes"]
+            assert st["warps"] > 0 and 0 < st["lane_steps"] <= 32 * st["warp_steps"]
             # caller-supplied rays take the same path
             assert tr.trace_rays(rays).tobytes() == hits.tobytes()
             frame = tr.run()

@@ -23,7 +23,20 @@ struct Hit {
 };
 struct Local {   // per-thread work counters
   uint32_t rays, box, tri, blas, shaded, err;
+  uint32_t lane_steps, warp_steps;   // traversal iterations of this lane / issued by this lane as its warp's leader
 };
+
+// One traversal iteration (a node fetch + its box tests, or one leaf) is about to run on the lanes converged here.
+// lane_steps / (32 * warp_steps) is the SIMT efficiency the simulator reports per RT unit (sim/simx/rt_unit.h:15-45,
+// rt_total_simt_efficiency / rt_total_warps).
+template <bool STATS>
+__device__ __forceinline__ void simt_step(Local &lc) {
+  if (STATS) {
+    unsigned m = __activemask();
+    lc.lane_steps++;
+    if ((threadIdx.x & 31u) == (unsigned)(__ffs(m) - 1)) lc.warp_steps++;
+  }
+}
 
 __device__ __forceinline__ float4 ldg4(const void *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
 
@@ -137,8 +150,10 @@ __device__ __forceinline__ Surface surface_at(const SceneA &sc, const Ray &ray, 
 __device__ __forceinline__ void flush_counters(WorkCounters *c, const Local &lc, bool stats) {
   unsigned rays = __reduce_add_sync(0xffffffffu, lc.rays);
   unsigned err = __reduce_or_sync(0xffffffffu, lc.err);
-  unsigned box = 0, tri = 0, blas = 0, shaded = 0;
+  unsigned box = 0, tri = 0, blas = 0, shaded = 0, lsteps = 0, wsteps = 0;
   if (stats) {
+    lsteps = __reduce_add_sync(0xffffffffu, lc.lane_steps);
+    wsteps = __reduce_add_sync(0xffffffffu, lc.warp_steps);
     box = __reduce_add_sync(0xffffffffu, lc.box);
     tri = __reduce_add_sync(0xffffffffu, lc.tri);
     blas = __reduce_add_sync(0xffffffffu, lc.blas);
@@ -152,6 +167,9 @@ __device__ __forceinline__ void flush_counters(WorkCounters *c, const Local &lc,
       atomicAdd(&c->tri_tests, (unsigned long long)tri);
       atomicAdd(&c->blas_entered, (unsigned long long)blas);
       atomicAdd(&c->shaded_hits, (unsigned long long)shaded);
+      atomicAdd(&c->lane_steps, (unsigned long long)lsteps);
+      atomicAdd(&c->warp_steps, (unsigned long long)wsteps);
+      atomicAdd(&c->warps, 1ull);
     }
   }
 }

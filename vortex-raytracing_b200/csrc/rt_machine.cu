@@ -284,11 +284,15 @@ __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &
       unsigned m = __ballot_sync(0xffffffffu, inner);
       if ((uint32_t)__popc(m) < inner_quorum) break;
       if (inner) {
+        simt_step<STATS>(lc);
         if (STRICT) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);   // the reference's own BVH2 walk
         else step_wide<STATS>(L, careful, stk_e, stk_d, lc);                        // 4-wide records (the launch guarantees sc.wide)
       }
     }
-    if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
+    if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) {
+      simt_step<STATS>(lc);
+      step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
+    }
     unsigned t = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
     if ((uint32_t)__popc(t) < quorum) return;
   }

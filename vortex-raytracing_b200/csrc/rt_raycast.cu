@@ -53,6 +53,7 @@ __device__ __forceinline__ bool blas_intersect(const SceneA &sc, uint32_t blasId
   uint32_t sp = 0;
   uint32_t cur = (kIndirect << 28) | 0u;   // root: node 0 of this BLAS, read on entry
   for (;;) {
+    simt_step<STATS>(lc);
     uint32_t kind = cur >> 28, first = cur & kPayloadMask, count = kind;
     if (kind == kIndirect) {
       const uint8_t *n = nodes + (size_t)first * sizeof(BvhNodeA);
@@ -132,6 +133,7 @@ __device__ __forceinline__ bool tlas_intersect(const SceneA &sc, const Ray &ray,
   const f3 id = mk3(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
   const bool nan_safe = isinf(id.x) || isinf(id.y) || isinf(id.z) || isnan(id.x) || isnan(id.y) || isnan(id.z);
   for (;;) {
+    simt_step<STATS>(lc);
     const uint8_t *n = reinterpret_cast<const uint8_t *>(sc.tlas + nodeIdx);
     float4 a = ldg4(n), b = ldg4(n + 16);
     uint32_t leftRight = __float_as_uint(a.w);

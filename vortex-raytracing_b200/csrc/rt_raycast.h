@@ -37,6 +37,7 @@ struct Partition {
 struct WorkCounters {       // device-resident, zeroed before each run
   unsigned long long rays, box_tests, tri_tests, blas_entered, shaded_hits;
   unsigned long long errors;   // bit 0: a traversal stack overflowed (the run is reported as failed)
+  unsigned long long lane_steps, warp_steps, warps;   // statistics mode: SIMT efficiency = lane_steps / (32 * warp_steps)
 };
 
 struct RenderA {

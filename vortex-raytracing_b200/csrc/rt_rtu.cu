@@ -185,6 +185,7 @@ __device__ __forceinline__ void trace_fast(const RtuScene &sc, const Ray &wray, 
   uint32_t cur = kTlasBit | 0u;                       // TLAS node 0 (calcNodePtr(tlas_ptr, 0), :41)
   float unused;
   for (;;) {
+    simt_step<STATS>(lc);
     const bool top = (cur & kTlasBit) != 0;
     const uint32_t idx = cur & ~kTlasBit;
     bool ok = top ? (idx < sc.n_tlas) : (idx < sc.n_bvh);
@@ -306,6 +307,7 @@ __device__ __forceinline__ bool strict_traverse(const RtuScene &sc, const Ray &w
   in.base = 0, in.blasIdx = 0, in.ray = world;
   bool done = false;
   while (!done) {
+    simt_step<STATS>(lc);
     const bool in_tlas_buf = (cur & kTlasBit) != 0;
     const uint32_t idx = cur & ~kTlasBit;
     if (!(in_tlas_buf ? (idx < sc.n_tlas) : (idx < sc.n_bvh))) {   // hostile index: treat as an empty inner node

@@ -429,6 +429,9 @@ private:
     stats_.tri_tests = h_counters_->tri_tests;
     stats_.blas_entered = h_counters_->blas_entered;
     stats_.shaded_hits = h_counters_->shaded_hits;
+    stats_.lane_steps = h_counters_->lane_steps;
+    stats_.warp_steps = h_counters_->warp_steps;
+    stats_.warps = h_counters_->warps;
     if (h_counters_->errors) return fail("run failed on the device: traversal stack overflow (error bits 0x%llx)", (unsigned long long)h_counters_->errors);
     stats_.kernel_launches = launches_;
     stats_.prep_launches = prep_launches_;
@@ -921,6 +924,12 @@ VXB_EXPORT int vx_dump_perf(vx_device_h hdevice, FILE *stream) {
   if (s.box_tests || s.tri_tests)
     fprintf(stream, "PERF: box_tests=%llu, tri_tests=%llu, blas_entered=%llu, shaded_hits=%llu\n", (unsigned long long)s.box_tests,
             (unsigned long long)s.tri_tests, (unsigned long long)s.blas_entered, (unsigned long long)s.shaded_hits);
+  // the RT unit's own summary (sim/simx/rt_unit.cpp print_stats: SIMT efficiency, warps, per-thread latency), in
+  // traversal steps instead of simulated cycles
+  if (s.warp_steps)
+    fprintf(stream, "PERF: rt: warps=%llu, warp_steps=%llu, thread_steps=%llu, simt_efficiency=%.4f, steps_per_ray=%.2f\n",
+            (unsigned long long)s.warps, (unsigned long long)s.warp_steps, (unsigned long long)s.lane_steps,
+            (double)s.lane_steps / (32.0 * (double)s.warp_steps), s.rays ? (double)s.lane_steps / (double)s.rays : 0.0);
   return 0;
 }
 

@@ -36,7 +36,8 @@ class VxError(RuntimeError):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64), ("blas_entered", C.c_uint64),
                 ("shaded_hits", C.c_uint64), ("kernel_launches", C.c_uint64), ("prep_launches", C.c_uint64),
-                ("kernel_ms", C.c_float), ("prep_ms", C.c_float)]
+                ("kernel_ms", C.c_float), ("prep_ms", C.c_float),
+                ("lane_steps", C.c_uint64), ("warp_steps", C.c_uint64), ("warps", C.c_uint64)]
 
 
 _lib = None
