@@ -194,6 +194,13 @@ int vx_b200_get_stats(vx_device_h hdevice, vx_b200_stats_t *stats);
 int vx_b200_trace_primary(vx_device_h hdevice, vx_buffer_h harguments, vx_buffer_h hhits);
 int vx_b200_trace_rays(vx_device_h hdevice, vx_buffer_h harguments, vx_buffer_h hrays, uint64_t count, vx_buffer_h hhits);
 
+/* The same records for rays and hits that live in HOST memory: equivalent to vx_copy_to_dev(rays) + vx_b200_trace_rays +
+ * vx_ready_wait + vx_copy_from_dev(hits), but processed in chunks (VORTEX_B200_HOST_CHUNK rays, default 2^20) whose upload,
+ * traversal and download legs overlap on separate streams, and without a device buffer for the whole batch.  Synchronous: the
+ * hit records are in `host_hits` on return.  Page-locked host memory is needed for the legs to overlap (pageable memory
+ * works, serialised by the driver's staging copies).  vx_b200_get_stats afterwards holds the sums over the chunks. */
+int vx_b200_trace_rays_host(vx_device_h hdevice, vx_buffer_h harguments, const void *host_rays, uint64_t count, void *host_hits);
+
 /* GPU BVH build: builds the layout-A BVH2 of `tri_count` triangles that already sit in `htri` (tri_t records
  * starting at triangle index tri_first) into `hbvh` (bvh_node_t records from node index node_first; 2*tri_count-1 are written)
  * and `htriIdx` (uint32 slots from slot_first; values are GLOBAL triangle indices tri_first+i in leaf order) — the byte layouts

@@ -106,7 +106,26 @@ def test_incoherent_and_edge_rays(oracle):
             tr.set_mode(0, strict)
             assert_hit_gates(hit_parity(tr.trace_rays(rays), ref_hits), strict)
         assert tr.dev.stats()["rays"] == len(rays)
+        # host-resident rays / records (vx_b200_trace_rays_host): same bytes as the buffer path for any chunking, ragged tail
+        # included; the statistics are the sums over the chunks
+        want = tr.trace_rays(rays)
+        for chunk in ("4096", "65536", None):
+            if chunk is None:
+                os.environ.pop("VORTEX_B200_HOST_CHUNK", None)
+            else:
+                os.environ["VORTEX_B200_HOST_CHUNK"] = chunk
+            got = tr.trace_rays_host(rays)
+            assert got.tobytes() == want.tobytes(), chunk
+            assert tr.dev.stats()["rays"] == len(rays)
+        assert tr.trace_rays_host(rays[:1]).tobytes() == want[:1].tobytes()
+        assert len(tr.trace_rays_host(rays[:0])) == 0
+        import torch
+        pr = torch.from_numpy(rays).pin_memory()
+        ph = torch.empty(len(rays) * 24, dtype=torch.uint8).pin_memory()
+        tr.dev.trace_rays_host(tr.args, pr.data_ptr(), len(rays), ph.data_ptr())
+        assert ph.numpy().tobytes() == want.tobytes()
     finally:
+        os.environ.pop("VORTEX_B200_HOST_CHUNK", None)
         tr.close()
 
 

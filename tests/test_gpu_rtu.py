@@ -62,8 +62,13 @@ def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
                 # RT-unit style counters: one traversal step per node the reference reads
                 assert st["lane_steps"] == work["nodes"]
             assert st["warps"] > 0 and 0 < st["lane_steps"] <= 32 * st["warp_steps"]
-            # caller-supplied rays take the same path
+            # caller-supplied rays take the same path, from a device buffer or straight from host memory in chunks
             assert tr.trace_rays(rays).tobytes() == hits.tobytes()
+            os.environ["VORTEX_B200_HOST_CHUNK"] = "4096"
+            try:
+                assert tr.trace_rays_host(rays).tobytes() == hits.tobytes()
+            finally:
+                os.environ.pop("VORTEX_B200_HOST_CHUNK", None)
             frame = tr.run()
             d = channel_diff(frame, want_frame)
             assert d <= (0 if strict else 1), (strict, d, int((frame != want_frame).sum()))

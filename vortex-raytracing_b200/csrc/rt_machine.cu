@@ -539,6 +539,7 @@ int launch_m(const RenderA &p, int num_sms, cudaStream_t stream) {
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, 0);
   if (e != cudaSuccess) return -(int)e;
   if (per_sm < 1) per_sm = 1;
+  if (p.blocks_per_sm_cap && per_sm > (int)p.blocks_per_sm_cap) per_sm = (int)p.blocks_per_sm_cap;
   kern<<<num_sms * per_sm, kBlockThreads, 0, stream>>>(p);
   e = cudaGetLastError();
   return e == cudaSuccess ? 1 : -(int)e;

@@ -52,6 +52,7 @@ struct RenderA {
   int stats;                // gather box/tri/blas counters
   uint32_t quorum_refill;   // ray state machine: run GEN/POST when fewer lanes than this are traversing
   uint32_t chunk;           //                    pixels a warp reserves per atomicAdd on the work counter
+  uint32_t blocks_per_sm_cap;   //                resident blocks per SM to launch (0 = as many as fit)
   uint32_t quorum_inner;    //                    leave the inner-node loop when fewer lanes than this hold an inner node
   // hit-record mode of the state machine (launch_trace_machine): closest-hit records instead of pixels
   const float *rays;        // 6 floats per ray, or nullptr => primary rays of `arg`

@@ -110,6 +110,8 @@ public:
     wide_ = nullptr, wide_bases_ = nullptr, wide_valid_ = false;
     if (rtu_nodes_) cudaFree(rtu_nodes_);
     if (rtu_tri_) cudaFree(rtu_tri_);
+    pipe_free_locked();
+    alt_free_locked();
     if (counters_) cudaFree(counters_);
     if (tile_counter_) cudaFree(tile_counter_);
     if (h_counters_) cudaFreeHost(h_counters_);
@@ -244,6 +246,85 @@ public:
       return trace_rtu_locked(args, rays_addr, count, hits_addr);
     if (args.size() < sizeof(KernelArgA)) return fail("trace: argument block too small");
     return start_raycast_locked(args, &hits_addr, rays_addr, count, 1);
+  }
+
+  // Host-resident rays in, host-resident hit records out: the same result as vx_copy_to_dev(rays) + vx_b200_trace_rays +
+  // vx_ready_wait + vx_copy_from_dev(hits), with the three legs of consecutive chunks overlapped (PCIe is full duplex):
+  //   upload stream:   H2D(i+1)            compute streams:   trace kernels(i-3 .. i)    download stream:   D2H(i-1 ..)
+  // kPipeSlots staging slots; a slot's rays may be overwritten once its kernel finished, its hits once they were downloaded.
+  // A launch over incoherent rays ends with a ~0.15 ms tail (its slowest rays, profiles/r01_sweep_host_trace.txt), so the
+  // chunks rotate over kRunCtxs run contexts (stream + counters + events each): one chunk's tail runs under the next ones.
+  int trace_host(uint64_t args_addr, const void *host_rays, uint64_t count, void *host_hits) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    std::vector<uint8_t> args;
+    if (fetch_args_locked(args_addr, args) != 0) return -1;
+    const bool layout_b = args.size() >= sizeof(KernelArgB) || dcr_get(VX_DCR_B200_RT_LAYOUT) == 2;
+    if (!layout_b && args.size() < sizeof(KernelArgA)) return fail("trace: argument block too small");
+    uint64_t chunk = env_u64("VORTEX_B200_HOST_CHUNK", 1ull << 20);   // sweep: profiles/r01_sweep_host_trace.txt
+    if (chunk < 4096 || chunk > (1ull << 24)) chunk = 1ull << 20;
+    if (chunk > count) chunk = (count + 31) & ~31ull;
+    if (run_pending_) {
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+    }
+    if (pipe_init_locked(chunk) != 0) return -1;
+    const uint64_t n_chunks = (count + chunk - 1) / chunk;
+    const uint8_t *src = (const uint8_t *)host_rays;
+    uint8_t *dst = (uint8_t *)host_hits;
+    auto upload = [&](uint64_t i) -> int {
+      int slot = (int)(i % kPipeSlots);
+      uint64_t off = i * chunk, n = std::min(chunk, count - off);
+      CUDA_TRY(cudaStreamWaitEvent(pipe_.s_up, pipe_.done[slot], 0));   // the kernel that last read this slot's rays finished
+      CUDA_TRY(cudaMemcpyAsync(pipe_.rays[slot], src + off * 24, n * 24, cudaMemcpyHostToDevice, pipe_.s_up));
+      CUDA_TRY(cudaEventRecord(pipe_.up[slot], pipe_.s_up));
+      return 0;
+    };
+    vx_b200_stats_t total{};
+    auto settle = [&]() -> int {   // wait for the chunk in flight on the current run context and add its counters
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+      total.rays += stats_.rays, total.box_tests += stats_.box_tests, total.tri_tests += stats_.tri_tests;
+      total.blas_entered += stats_.blas_entered, total.shaded_hits += stats_.shaded_hits;
+      total.kernel_launches += stats_.kernel_launches, total.prep_launches += stats_.prep_launches;
+      total.kernel_ms += stats_.kernel_ms, total.prep_ms += stats_.prep_ms;
+      total.lane_steps += stats_.lane_steps, total.warp_steps += stats_.warp_steps, total.warps += stats_.warps;
+      return 0;
+    };
+    auto body = [&]() -> int {
+      if (upload(0) != 0) return -1;
+      for (uint64_t i = 0; i < n_chunks; i++) {
+        int slot = (int)(i % kPipeSlots);
+        uint64_t off = i * chunk, n = std::min(chunk, count - off);
+        if (i + 1 < n_chunks && upload(i + 1) != 0) return -1;
+        use_ctx_locked((int)(i % kRunCtxs));            // chunks rotate over the run contexts
+        if (run_pending_ && settle() != 0) return -1;   // chunk i - kRunCtxs
+        CUDA_TRY(cudaStreamWaitEvent(stream_, pipe_.up[slot], 0));
+        CUDA_TRY(cudaStreamWaitEvent(stream_, pipe_.down[slot], 0));    // the hit records that last sat in this slot were downloaded
+        pipe_rays_ = pipe_.rays[slot], pipe_hits_ = pipe_.hits[slot];
+        uint64_t zero = 0;
+        int rc = layout_b ? trace_rtu_locked(args, &zero, n, 0) : start_raycast_locked(args, &zero, &zero, n, 1);
+        pipe_rays_ = nullptr, pipe_hits_ = nullptr;
+        if (rc != 0) return -1;
+        if (i == 0)   // scene records (re)built by chunk 0 are visible to the other contexts
+          for (int c = 1; c < kRunCtxs; c++) CUDA_TRY(cudaStreamWaitEvent(ctx_[c].stream, ev_prep_, 0));
+        CUDA_TRY(cudaEventRecord(pipe_.done[slot], stream_));
+        CUDA_TRY(cudaStreamWaitEvent(pipe_.s_down, pipe_.done[slot], 0));
+        CUDA_TRY(cudaMemcpyAsync(dst + off * sizeof(HitA), pipe_.hits[slot], n * sizeof(HitA), cudaMemcpyDeviceToHost, pipe_.s_down));
+        CUDA_TRY(cudaEventRecord(pipe_.down[slot], pipe_.s_down));
+      }
+      return 0;
+    };
+    int rc = body();
+    for (int c = kRunCtxs - 1; c >= 0; c--) {   // ends on the device's own context
+      use_ctx_locked(c);
+      if (run_pending_ && settle() != 0) rc = -1;
+    }
+    cudaStreamSynchronize(pipe_.s_up);
+    CUDA_TRY(cudaStreamSynchronize(pipe_.s_down));
+    if (rc != 0) return -1;
+    stats_ = total;   // kernel_ms is the sum over chunks; consecutive chunks overlap, so it exceeds the wall time of the call
+    return 0;
   }
 
   int ready_wait(uint64_t timeout_ms) {
@@ -468,8 +549,12 @@ private:
       }
     } else {
       uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
-      if (resolve(*hits_addr, n * sizeof(HitA), 4, "hits", &hits)) return -1;
-      if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &rays)) return -1;
+      if (pipe_hits_) {   // chunk of vx_b200_trace_rays_host: staging buffers outside the arena
+        hits = pipe_hits_, rays = pipe_rays_;
+      } else {
+        if (resolve(*hits_addr, n * sizeof(HitA), 4, "hits", &hits)) return -1;
+        if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &rays)) return -1;
+      }
       count = n;
     }
     if (begin_run_locked() != 0) return -1;
@@ -578,6 +663,9 @@ private:
         if (p.quorum_refill < 2 || p.quorum_refill > 32) p.quorum_refill = 16;
         if (p.quorum_inner < 1 || p.quorum_inner >= p.quorum_refill) p.quorum_inner = p.quorum_refill / 2;
         p.rays = rays, p.hits = hits, p.count = count;
+        // chunk of the host pipeline: kRunCtxs kernels share the SMs, so that one chunk's tail (its slowest rays) runs
+        // under the other chunks' bodies instead of idling the device
+        if (pipe_hits_) p.blocks_per_sm_cap = (uint32_t)env_u64("VORTEX_B200_HOST_BLOCKS_PER_SM", 2);
         rc = launch_trace_machine(p, prop_.multiProcessorCount, stream_);
       }
     }
@@ -668,9 +756,13 @@ private:
     memcpy(&a, args.data(), sizeof(a));
     RtuTrace p{};
     uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
-    if (resolve(hits_addr, n * sizeof(HitA), 4, "hits", &p.hits)) return -1;
     p.rays = nullptr;
-    if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &p.rays)) return -1;
+    if (pipe_hits_) {
+      p.hits = pipe_hits_, p.rays = pipe_rays_;
+    } else {
+      if (resolve(hits_addr, n * sizeof(HitA), 4, "hits", &p.hits)) return -1;
+      if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &p.rays)) return -1;
+    }
     if (begin_run_locked() != 0) return -1;
     if (rtu_scene_locked(a, &p.scene)) return -1;
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
@@ -680,6 +772,90 @@ private:
     if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
     launches_ += rc;
     return end_run_locked();
+  }
+
+  // ---- vx_b200_trace_rays_host: rays and hit records stay in host memory, chunks are pipelined over upload / compute / download streams ----
+  static constexpr int kPipeSlots = 6;
+  struct HostPipe {
+    float *rays[kPipeSlots] = {};
+    HitA *hits[kPipeSlots] = {};
+    cudaEvent_t up[kPipeSlots] = {}, done[kPipeSlots] = {}, down[kPipeSlots] = {};
+    cudaStream_t s_up = nullptr, s_down = nullptr;
+    uint64_t cap = 0;   // rays per slot
+  } pipe_;
+  const float *pipe_rays_ = nullptr;   // staging slot of the chunk being launched (null outside trace_host)
+  HitA *pipe_hits_ = nullptr;
+
+  int pipe_init_locked(uint64_t chunk) {
+    if (pipe_.cap >= chunk) return 0;
+    pipe_free_locked();
+    CUDA_TRY(cudaStreamCreateWithFlags(&pipe_.s_up, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&pipe_.s_down, cudaStreamNonBlocking));
+    for (int i = 0; i < kPipeSlots; i++) {
+      CUDA_TRY(cudaMalloc(&pipe_.rays[i], chunk * 24));
+      CUDA_TRY(cudaMalloc(&pipe_.hits[i], chunk * sizeof(HitA)));
+      CUDA_TRY(cudaEventCreateWithFlags(&pipe_.up[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&pipe_.done[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&pipe_.down[i], cudaEventDisableTiming));
+    }
+    pipe_.cap = chunk;
+    for (int c = 1; c < kRunCtxs; c++) {   // extra run contexts: the kernels of consecutive chunks overlap (tail of one under the others)
+      RunCtx &x = ctx_[c];
+      if (x.stream) continue;
+      CUDA_TRY(cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking));
+      CUDA_TRY(cudaMalloc(&x.counters, sizeof(WorkCounters)));
+      CUDA_TRY(cudaMalloc(&x.tile_counter, sizeof(uint32_t)));
+      CUDA_TRY(cudaMallocHost(&x.h_counters, sizeof(WorkCounters)));
+      CUDA_TRY(cudaEventCreate(&x.ev_begin));
+      CUDA_TRY(cudaEventCreate(&x.ev_prep));
+      CUDA_TRY(cudaEventCreate(&x.ev_end));
+    }
+    return 0;
+  }
+  void pipe_free_locked() {
+    for (int i = 0; i < kPipeSlots; i++) {
+      if (pipe_.rays[i]) cudaFree(pipe_.rays[i]);
+      if (pipe_.hits[i]) cudaFree(pipe_.hits[i]);
+      if (pipe_.up[i]) cudaEventDestroy(pipe_.up[i]);
+      if (pipe_.done[i]) cudaEventDestroy(pipe_.done[i]);
+      if (pipe_.down[i]) cudaEventDestroy(pipe_.down[i]);
+    }
+    if (pipe_.s_up) cudaStreamDestroy(pipe_.s_up);
+    if (pipe_.s_down) cudaStreamDestroy(pipe_.s_down);
+    pipe_ = HostPipe{};
+  }
+  static constexpr int kRunCtxs = 4;
+  struct RunCtx {
+    cudaStream_t stream = nullptr;
+    WorkCounters *counters = nullptr, *h_counters = nullptr;
+    uint32_t *tile_counter = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_prep = nullptr, ev_end = nullptr;
+    bool run_pending = false;
+    uint64_t launches = 0, prep_launches = 0;
+  } ctx_[kRunCtxs];      // [0] is only a parking slot for the device's own context while another one is loaded
+  int cur_ctx_ = 0;
+  void use_ctx_locked(int k) {
+    if (k == cur_ctx_) return;
+    ctx_[cur_ctx_] = RunCtx{stream_, counters_, h_counters_, tile_counter_, ev_begin_, ev_prep_, ev_end_, run_pending_, launches_, prep_launches_};
+    const RunCtx &x = ctx_[k];
+    stream_ = x.stream, counters_ = x.counters, h_counters_ = x.h_counters, tile_counter_ = x.tile_counter;
+    ev_begin_ = x.ev_begin, ev_prep_ = x.ev_prep, ev_end_ = x.ev_end, run_pending_ = x.run_pending;
+    launches_ = x.launches, prep_launches_ = x.prep_launches;
+    cur_ctx_ = k;
+  }
+  void alt_free_locked() {
+    use_ctx_locked(0);
+    for (int c = 1; c < kRunCtxs; c++) {
+      RunCtx &x = ctx_[c];
+      if (x.stream) cudaStreamDestroy(x.stream);
+      if (x.counters) cudaFree(x.counters);
+      if (x.tile_counter) cudaFree(x.tile_counter);
+      if (x.h_counters) cudaFreeHost(x.h_counters);
+      if (x.ev_begin) cudaEventDestroy(x.ev_begin);
+      if (x.ev_prep) cudaEventDestroy(x.ev_prep);
+      if (x.ev_end) cudaEventDestroy(x.ev_end);
+      x = RunCtx{};
+    }
   }
 
   std::mutex mu_;
@@ -1032,5 +1208,10 @@ VXB_EXPORT int vx_b200_trace_rays(vx_device_h h, vx_buffer_h harguments, vx_buff
   if (count == 0) return 0;
   uint64_t ra = ((Buffer *)hrays)->addr;
   return ((Device *)h)->trace(((Buffer *)harguments)->addr, &ra, count, ((Buffer *)hhits)->addr);
+}
+VXB_EXPORT int vx_b200_trace_rays_host(vx_device_h h, vx_buffer_h harguments, const void *host_rays, uint64_t count, void *host_hits) {
+  if (!h || !harguments || !host_rays || !host_hits) return -1;
+  if (count == 0) return 0;
+  return ((Device *)h)->trace_host(((Buffer *)harguments)->addr, host_rays, count, host_hits);
 }
 VXB_EXPORT const char *vx_b200_last_error(void) { return vxb::g_last_error.c_str(); }

@@ -122,6 +122,17 @@ class RtxTracer:
             rb.free()
         return out
 
+    def trace_rays_host(self, rays, out=None):
+        """the same hit records with rays and records left in host memory (vx_b200_trace_rays_host: chunked, pipelined)"""
+        self._upload_args()
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        if out is None:
+            out = np.empty(n, dtype=HIT_DT)
+        if n:
+            self.dev.trace_rays_host(self.args, rays.ctypes.data, n, out.ctypes.data)
+        return out
+
     def set_order(self, strict_order=False):
         self.dev.dcr_write(vx.VX_DCR_B200_RT_ORDER, int(bool(strict_order)))
 

@@ -25,7 +25,7 @@ EXPORTS = (
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
     "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
-    "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_last_error"
+    "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_trace_rays_host vx_b200_last_error"
 ).split()
 
 
@@ -65,6 +65,7 @@ def lib():
             "vx_b200_stream": [H, C.POINTER(u64)], "vx_b200_last_kernel_ms": [H, C.POINTER(C.c_float)],
             "vx_b200_enable_stats": [H, i32], "vx_b200_get_stats": [H, C.POINTER(Stats)],
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
+            "vx_b200_trace_rays_host": [H, B, C.c_void_p, u64, C.c_void_p],
             "vx_b200_build_bvh": [H, B, u64, u64, B, u64, B, u64, C.POINTER(u64)],
             "vx_b200_export_buffer": [B, vp, C.POINTER(u64)], "vx_b200_set_remote_framebuffer": [H, vp, u64, u64],
         }
@@ -246,6 +247,10 @@ class Device:
 
     def trace_rays(self, arguments, rays, count, hits):
         _check(lib().vx_b200_trace_rays(self.h, arguments.h, rays.h, count, hits.h), "vx_b200_trace_rays")
+
+    def trace_rays_host(self, arguments, rays_ptr, count, hits_ptr):
+        """rays / hit records in host memory (raw addresses), chunked and pipelined by the backend; synchronous"""
+        _check(lib().vx_b200_trace_rays_host(self.h, arguments.h, C.c_void_p(rays_ptr), count, C.c_void_p(hits_ptr)), "vx_b200_trace_rays_host")
 
 
 # a minimal stand-in for kernel.vxbin: {min_vma, max_vma} header + 1 byte (runtime/stub/utils.cpp:25-61).
