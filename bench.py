@@ -641,6 +641,16 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
     tr.set_order(0)
     tr.launch()
     unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(wk, "strict")]
+    # the same frame through the traceRay/getWork/getAttr/commit shim with the shipped shaders dispatched by SBT
+    tr.dev.enable_stats(False)
+    tr.set_program(0)
+    pms = []
+    for i in range(steps + 2):
+        tr.launch()
+        if i >= 2:
+            pms.append(tr.dev.last_kernel_ms())
+    tr.set_program(None)
+    program_ms = float(np.mean(pms))
     tr.close()
     abytes = 52 * wk["box_tests"] + 52 * wk["blas_entered"] + 36 * wk["tri_tests"] + 156 * wk["shaded_hits"] + 4 * w * h
     k_ms = float(np.mean(ms))
@@ -651,6 +661,8 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
            "work_per_ray": {"nodes": wk["box_tests"] / max(1, rays), "tri_tests": wk["tri_tests"] / max(1, rays),
                             "blas_entered": wk["blas_entered"] / max(1, rays), "shaded_hits": wk["shaded_hits"] / max(1, rays)},
            "rt_unit_perf": unit_perf,
+           "shader_program_kernel": {"kernel": "k_rtu_program<ShippedShaders> (fast order)", "kernel_ms": program_ms,
+                                     "mrays_per_s": rays / (program_ms * 1e3)},
            "note": "kernel time only, L2 not flushed; algorithmic work = the reference's trail/short-stack order (strict)"}
     if with_cpu:
         R = importlib.import_module("oracle.pyoracle_rtu")

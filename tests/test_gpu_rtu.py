@@ -78,6 +78,17 @@ def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
                 if ref_hits is not None:   # outputs of the compiled reference recorded in the fixture
                     assert hits.tobytes() == ref_hits.tobytes()
                     assert np.array_equal(frame, ref_image)
+            # the three shipped shaders restated against the traceRay/getWork/getAttr/commit shim and dispatched through the
+            # SBT: the same frame and the same work as the fused kernel, in either order
+            fused = tr.dev.stats()
+            tr.set_program(0)
+            try:
+                assert np.array_equal(tr.run(), frame)
+                prog = tr.dev.stats()
+                for k in ("rays", "box_tests", "tri_tests", "blas_entered", "shaded_hits"):
+                    assert prog[k] == fused[k], (k, strict, prog[k], fused[k])
+            finally:
+                tr.set_program(None)
         if R.have_ref():
             ok = flags == 0
             h_ref = R.RtuRef().trace_rays(img, rays[ok], threads=threads)
@@ -138,3 +149,47 @@ def test_rtu_full_size_fast_equals_strict():
         assert (hf["dist"] < 1e30).mean() > 0.2
     finally:
         tr.close()
+
+
+def test_rtu_any_hit_cut_out():
+    """an any-hit shader that answers VX_RT_COMMIT_CONT (program 1: triangles of odd index are cut out) — the path the shipped
+    any-hit never takes.  Oracle: the same scene with the odd triangles collapsed to points (Moller-Trumbore rejects them,
+    the boxes stay conservative), rendered by the shipped shaders on the GPU and by the port on the CPU."""
+    import importlib
+    from rt_common import scenes
+    from rtu_common import b_mesh
+    host = importlib.import_module("vortex-raytracing_b200.host")
+    hs = host.RtxHostScene([b_mesh(scenes.heightfield(24), two_materials=True),
+                            b_mesh(scenes.icosphere((0, 0.5, 0), 0.4, 2), diffuse=(0.2, 0.6, 0.9), reflectivity=0.5)])
+    karg = hs.setup(160, 120, max_depth=3)
+    bufs = hs.buffers()
+    cut = dict(bufs)
+    tri = bufs["tri"].view(np.float32).reshape(-1, 9).copy()
+    tri[1::2, 3:6] = tri[1::2, 0:3]
+    tri[1::2, 6:9] = tri[1::2, 0:3]
+    cut["tri"] = tri.reshape(-1).view(np.uint8)
+    tr = tracer_b(bufs, karg, 1)
+    tr2 = tracer_b(cut, karg, 1)
+    try:
+        tr.set_program(1)
+        got = tr.run().copy()
+        tr2.set_program(0)
+        want = tr2.run().copy()
+        assert np.array_equal(got, want)
+        tr.set_program(0)
+        assert not np.array_equal(tr.run(), got)          # the cut-out changes the picture
+        port = R.RtuPort()
+        port.set_fix_tlas_base(1)
+        try:
+            frame_port = port.render(R.Image(cut, karg), 1, threads=os.cpu_count() or 1)
+        finally:
+            port.set_fix_tlas_base(0)
+        assert channel_diff(got, frame_port) <= 1
+        # strict order cannot ignore a candidate (the reference would re-find it forever): reported as a failed run
+        tr.set_program(1)
+        tr.set_order(1)
+        with pytest.raises(Exception):
+            tr.run()
+    finally:
+        tr.close()
+        tr2.close()

@@ -574,6 +574,9 @@ __global__ void __launch_bounds__(kBlockThreads) k_rtu_trace(const __grid_consta
   flush_counters(p.counters, lc, STATS);
 }
 
+#include "vx_raytrace_b200.cuh"
+#include "rt_rtu_programs.cuh"
+
 template <class K, class P>
 int launch_persistent(K kern, const P &p, int num_sms, cudaStream_t stream, uint64_t want_blocks) {
   int per_sm = 0;
@@ -605,6 +608,33 @@ int launch_rtu_render(const RtuRender &p, int num_sms, cudaStream_t stream) {
                                      : launch_persistent(k_rtu_render<true, false>, p, num_sms, stream, 0);
   return p.stats ? launch_persistent(k_rtu_render<false, true>, p, num_sms, stream, 0)
                  : launch_persistent(k_rtu_render<false, false>, p, num_sms, stream, 0);
+}
+
+namespace {
+template <class P>
+int launch_program_t(const RtuRender &p, int num_sms, cudaStream_t stream) {
+  if (p.strict_order) return p.stats ? launch_persistent(k_rtu_program<P, true, true>, p, num_sms, stream, 0)
+                                     : launch_persistent(k_rtu_program<P, true, false>, p, num_sms, stream, 0);
+  return p.stats ? launch_persistent(k_rtu_program<P, false, true>, p, num_sms, stream, 0)
+                 : launch_persistent(k_rtu_program<P, false, false>, p, num_sms, stream, 0);
+}
+}  // namespace
+
+// shader programs over the traceRay/getWork/getAttr/commit shim (vx_raytrace_b200.cuh); `program` indexes rt_rtu_programs.cuh
+int launch_rtu_program(const RtuRender &p, uint32_t program, int num_sms, cudaStream_t stream) {
+  // the closest-hit shader recurses through the SBT for mirror rays: give the device stack room for kMaxBounce frames
+  static bool stack_set = false;
+  if (!stack_set) {
+    size_t cur = 0;
+    cudaDeviceGetLimit(&cur, cudaLimitStackSize);
+    if (cur < 12288) cudaDeviceSetLimit(cudaLimitStackSize, 12288);
+    stack_set = true;
+  }
+  switch (program) {
+    case 0: return launch_program_t<ShaderSet<false>>(p, num_sms, stream);
+    case 1: return launch_program_t<ShaderSet<true>>(p, num_sms, stream);
+    default: return -(int)cudaErrorInvalidValue;
+  }
 }
 
 int launch_rtu_trace(const RtuTrace &p, int num_sms, cudaStream_t stream) {

@@ -67,6 +67,7 @@ cudaError_t launch_rtu_decode_nodes(const QNodeB *nodes, GpuNodeB *out, uint64_t
 cudaError_t launch_rtu_gather_tris(const TriA *tri, GpuTri *gtri, uint64_t n, cudaStream_t stream);
 // return the number of kernels launched (>0) or a negative cudaError_t
 int launch_rtu_render(const RtuRender &p, int num_sms, cudaStream_t stream);
+int launch_rtu_program(const RtuRender &p, uint32_t program, int num_sms, cudaStream_t stream);   // returns launches or -cudaError
 int launch_rtu_trace(const RtuTrace &p, int num_sms, cudaStream_t stream);
 
 }  // namespace vxb

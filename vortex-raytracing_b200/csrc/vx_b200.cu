@@ -513,7 +513,7 @@ private:
     stats_.lane_steps = h_counters_->lane_steps;
     stats_.warp_steps = h_counters_->warp_steps;
     stats_.warps = h_counters_->warps;
-    if (h_counters_->errors) return fail("run failed on the device: traversal stack overflow (error bits 0x%llx)", (unsigned long long)h_counters_->errors);
+    if (h_counters_->errors) return fail("run failed on the device (error bits 0x%llx: 1 traversal stack overflow, 2 traceRay nesting too deep, 4 COMMIT_CONT in strict order)", (unsigned long long)h_counters_->errors);
     stats_.kernel_launches = launches_;
     stats_.prep_launches = prep_launches_;
     stats_.prep_ms = ms_prep;
@@ -744,7 +744,11 @@ private:
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.part = part_, p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
     p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
-    int rc = launch_rtu_render(p, prop_.multiProcessorCount, stream_);
+    // VX_DCR_B200_RT_KERNEL: 0 = the fused kernel; 2 + n = shader program n through the traceRay/getWork/getAttr/commit
+    // shim (vx_raytrace_b200.cuh; program 0 = the three shipped shaders, rt_rtu_programs.cuh)
+    uint32_t kernel = dcr_get(VX_DCR_B200_RT_KERNEL);
+    int rc = kernel >= 2 ? launch_rtu_program(p, kernel - 2, prop_.multiProcessorCount, stream_)
+                         : launch_rtu_render(p, prop_.multiProcessorCount, stream_);
     if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
     launches_ += rc;
     return end_run_locked();

@@ -136,6 +136,11 @@ class RtxTracer:
     def set_order(self, strict_order=False):
         self.dev.dcr_write(vx.VX_DCR_B200_RT_ORDER, int(bool(strict_order)))
 
+    def set_program(self, program=None):
+        """None = the fused kernel; n = shader program n written against the traceRay/getWork/getAttr/commit shim
+        (csrc/vx_raytrace_b200.cuh; 0 = the three shipped shaders, 1 = the cut-out any-hit demo)"""
+        self.dev.dcr_write(vx.VX_DCR_B200_RT_KERNEL, 0 if program is None else 2 + int(program))
+
     def close(self):
         for b in list(self.bufs.values()) + self.shaders + [self.out, self.args, self.krnl, self.sbt]:
             if b is not None:
