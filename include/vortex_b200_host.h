@@ -81,6 +81,38 @@ void vxh_rtx_setup(vxh_rtx_scene_h scene, void *kernel_arg_216, uint32_t width, 
                    float camera_vfov_deg, float zoom, const float *light_pos, const float *light_color, const float *ambient,
                    const float *background);
 
+/* ---- asset path: what the raytracing host reads and writes around the scene builder ----
+ * vxh_obj_load: Wavefront OBJ (+ its mtllib and the PNG textures its map_Kd statements name, looked up next to the .obj)
+ *   -> one mesh in exactly the arrays vxh_rtx_scene_create takes.  Mirrors Mesh::Mesh(objFile)
+ *   (tests/regression/raytracing/mesh.cpp:130-293): faces in file order, un-indexed vertices, quads split along the shorter
+ *   diagonal, larger polygons ear-clipped, texId = the face's material id (0 without one), missing normals / UVs = 0,
+ *   one texture per distinct map_Kd name; material_info_t.diffuse_tex_id / tex_width / tex_height as the reference sets them,
+ *   tex_offset = byte offset of the material's texture inside `tex`, reflectivity and illum-independent fields zero.
+ * vxh_png_load: 8-bit RGB texels packed 0x00RRGGBB like Surface::loadImage (surface.cpp:40-52); non-interlaced PNG of any
+ *   colour type / bit depth; alpha dropped.  *texels is malloc'ed: release with vxh_free.
+ * vxh_ppm_write: format 3 = the reference's text writer byte for byte when flip_vertical = 1 (tracer.cpp:15-33); format 6 =
+ *   binary PPM (the same picture, ~4x smaller and without the formatting cost that dominates the reference's wall time).
+ * Errors: NULL / non-zero, text in vxh_asset_last_error(). */
+typedef void *vxh_asset_mesh_h;
+typedef struct {
+  const float *tris;        /* 9 floats per triangle */
+  const uint32_t *triex16;  /* 16 words per triangle: N0 N1 N2 uv0 uv1 uv2 (floats) + texId */
+  uint32_t tri_count;
+  uint32_t n_mats;
+  const void *mats;         /* material_info_t[n_mats], 88 B each */
+  const uint8_t *tex;       /* the mesh's textures, concatenated, 4 B per texel */
+  uint64_t tex_bytes;
+  uint32_t n_textures, _pad;
+} vxh_asset_mesh_view_t;
+vxh_asset_mesh_h vxh_obj_load(const char *obj_path);
+void vxh_asset_mesh_view(vxh_asset_mesh_h mesh, vxh_asset_mesh_view_t *view);
+const char *vxh_asset_mesh_texture_name(vxh_asset_mesh_h mesh, uint32_t index);
+void vxh_asset_mesh_free(vxh_asset_mesh_h mesh);
+int vxh_png_load(const char *path, uint32_t *width, uint32_t *height, uint32_t **texels);
+void vxh_free(void *p);
+int vxh_ppm_write(const char *path, const uint32_t *pixels, uint32_t width, uint32_t height, int format, int flip_vertical);
+const char *vxh_asset_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

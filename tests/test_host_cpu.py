@@ -140,7 +140,7 @@ def test_host_library_exports():
     header = open(os.path.join(ROOT, "include", "vortex_b200_host.h")).read()
     header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
     declared = set(re.findall(r"\b(vxh_[a-z0-9_]+)\s*\(", header))
-    assert declared == set(host.EXPORTS) | set(host.RTX_EXPORTS)
+    assert declared == set(host.EXPORTS) | set(host.RTX_EXPORTS) | set(host.ASSET_EXPORTS)
     L = ctypes.CDLL(host.LIB_PATH)
     for n in declared:
         assert hasattr(L, n), n

@@ -217,3 +217,91 @@ class RtxHostScene:
             out[n] = np.frombuffer(C.string_at(getattr(v, n), nbytes), dtype=np.uint8).copy() if nbytes else np.zeros(0, np.uint8)
         out["bvh_nodes_used"], out["tlas_nodes_used"] = int(v.bvh_nodes_used), int(v.tlas_nodes_used)
         return out
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# asset path: OBJ/MTL/PNG in, PPM out — vortex-raytracing_b200/host/asset_io.cpp
+# ----------------------------------------------------------------------------------------------------------------------
+ASSET_EXPORTS = ("vxh_obj_load vxh_asset_mesh_view vxh_asset_mesh_texture_name vxh_asset_mesh_free vxh_png_load vxh_free "
+                 "vxh_ppm_write vxh_asset_last_error").split()
+
+
+class _AssetView(C.Structure):
+    _fields_ = [("tris", C.c_void_p), ("triex16", C.c_void_p), ("tri_count", C.c_uint32), ("n_mats", C.c_uint32),
+                ("mats", C.c_void_p), ("tex", C.c_void_p), ("tex_bytes", C.c_uint64), ("n_textures", C.c_uint32), ("_pad", C.c_uint32)]
+
+
+def _asset_lib():
+    L = lib()
+    if not getattr(L, "_asset_ready", False):
+        L.vxh_obj_load.restype = C.c_void_p
+        L.vxh_obj_load.argtypes = [C.c_char_p]
+        L.vxh_asset_mesh_view.argtypes = [C.c_void_p, C.POINTER(_AssetView)]
+        L.vxh_asset_mesh_view.restype = None
+        L.vxh_asset_mesh_texture_name.restype = C.c_char_p
+        L.vxh_asset_mesh_texture_name.argtypes = [C.c_void_p, C.c_uint32]
+        L.vxh_asset_mesh_free.argtypes = [C.c_void_p]
+        L.vxh_asset_mesh_free.restype = None
+        L.vxh_png_load.argtypes = [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]
+        L.vxh_free.argtypes = [C.c_void_p]
+        L.vxh_free.restype = None
+        L.vxh_ppm_write.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int]
+        L.vxh_asset_last_error.restype = C.c_char_p
+        L._asset_ready = True
+    return L
+
+
+def _asset_error(L, what):
+    raise RuntimeError(f"{what}: {L.vxh_asset_last_error().decode(errors='replace')}")
+
+
+def load_obj(path, reflectivity=0.0, transform=None):
+    """Mesh::Mesh(objFile) (raytracing/mesh.cpp:215-293): one mesh dict in the form RtxHostScene takes, plus the raw
+    material_info_t records and texture blob under 'mats_raw' / 'tex_raw' / 'texture_names'."""
+    L = _asset_lib()
+    h = L.vxh_obj_load(os.fsencode(path))
+    if not h:
+        _asset_error(L, f"vxh_obj_load({path})")
+    try:
+        v = _AssetView()
+        L.vxh_asset_mesh_view(h, C.byref(v))
+        n = int(v.tri_count)
+        tris = np.frombuffer(C.string_at(v.tris, n * 36), dtype=np.float32).reshape(n, 9).copy() if n else np.zeros((0, 9), np.float32)
+        ex = np.frombuffer(C.string_at(v.triex16, n * 64), dtype=np.uint32).reshape(n, 16).copy() if n else np.zeros((0, 16), np.uint32)
+        mats = np.frombuffer(C.string_at(v.mats, int(v.n_mats) * 88), dtype=MATERIAL_DT).copy() if v.n_mats else np.zeros(0, MATERIAL_DT)
+        tex = np.frombuffer(C.string_at(v.tex, int(v.tex_bytes)), dtype=np.uint8).copy() if v.tex_bytes else np.zeros(0, np.uint8)
+        names = [L.vxh_asset_mesh_texture_name(h, i).decode() for i in range(int(v.n_textures))]
+    finally:
+        L.vxh_asset_mesh_free(h)
+    materials = []
+    for m in mats:
+        if m["diffuse_tex_id"] >= 0:
+            w, hgt, off = int(m["tex_width"]), int(m["tex_height"]), int(m["tex_offset"])
+            materials.append({"tex": tex[off:off + 4 * w * hgt].view(np.uint32).reshape(hgt, w), "diffuse": tuple(m["diffuse"])})
+        else:
+            materials.append({"diffuse": tuple(float(x) for x in m["diffuse"])})
+    if not materials:   # an OBJ without a material library: every triangle has texId 0
+        materials = [{"diffuse": (0.6, 0.6, 0.6)}]
+    return {"tris": tris, "triex": ex[:, :15].view(np.float32).copy(), "texid": ex[:, 15].copy(), "materials": materials,
+            "reflectivity": float(reflectivity), "transform": transform, "mats_raw": mats, "tex_raw": tex, "texture_names": names}
+
+
+def load_png(path):
+    """Surface(file) for PNG (raytracing/surface.cpp:40-52): (h, w) uint32 texels 0x00RRGGBB"""
+    L = _asset_lib()
+    w, h, p = C.c_uint32(), C.c_uint32(), C.c_void_p()
+    if L.vxh_png_load(os.fsencode(path), C.byref(w), C.byref(h), C.byref(p)) != 0:
+        _asset_error(L, f"vxh_png_load({path})")
+    try:
+        return np.frombuffer(C.string_at(p, w.value * h.value * 4), dtype=np.uint32).reshape(h.value, w.value).copy()
+    finally:
+        L.vxh_free(p)
+
+
+def write_ppm(path, frame, binary=True, flip_vertical=True):
+    """frame: (h, w) uint32 0x00RRGGBB as the kernels write it.  binary=False reproduces the reference's P3 text file
+    (raytracing/tracer.cpp:15-33) byte for byte; binary=True is the same picture as P6."""
+    L = _asset_lib()
+    f = np.ascontiguousarray(frame, dtype=np.uint32)
+    if L.vxh_ppm_write(os.fsencode(path), f.ctypes.data, f.shape[1], f.shape[0], 6 if binary else 3, int(bool(flip_vertical))) != 0:
+        _asset_error(L, f"vxh_ppm_write({path})")
