@@ -211,6 +211,18 @@ int vx_b200_trace_rays_host(vx_device_h hdevice, vx_buffer_h harguments, const v
 int vx_b200_build_bvh(vx_device_h hdevice, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h hbvh,
                       uint64_t node_first, vx_buffer_h htriIdx, uint64_t slot_first, uint64_t *nodes_used);
 
+/* GPU BVH build for layout B (the RT unit's buffers): the same radix tree collapsed to a BVH4 and quantized into
+ * bvh_quantized_node_t records (52 B, raytracing/common.h:58-67; what BVH::build + quantize leave in qBvh, raytracing/bvh.cpp:
+ * 38-258) written to `hqbvh` from node index node_first; node indices inside the records are relative to node_first, which is
+ * what the host stores in blas_node_t.bvh_offset.  Layout B has no triangle index array, so the tri_t records [tri_first,
+ * tri_first+tri_count) of `htri` and the matching tri_ex_t records of `htriEx` (64 B each; may be NULL) are PERMUTED IN PLACE
+ * into leaf order; a leaf's leftFirst is the global index tri_first + position.  One-triangle leaves; every child box is
+ * verified to contain the child under the RT unit's own decode (origin + ldexp(q, e), rt_traversal.cpp:61-67).
+ * Synchronous.  *nodes_used = nodes written (<= 2*tri_count; the call fails if `hqbvh` is smaller), root_box6 (may be NULL) =
+ * the mesh's bounds {lo.xyz, hi.xyz} for the host's TLAS. */
+int vx_b200_build_qbvh(vx_device_h hdevice, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h htriEx,
+                       vx_buffer_h hqbvh, uint64_t node_first, uint64_t *nodes_used, float *root_box6);
+
 /* Human-readable description of the last error on this thread ("" if none). */
 const char *vx_b200_last_error(void);
 

@@ -86,3 +86,73 @@ def test_gpu_build_one_triangle_and_errors():
             tr.dev.build_bvh(tr.bufs["tri"], 5, tr.bufs["bvh"], tr.bufs["triIdx"])   # more triangles than the buffer holds
     finally:
         tr.close()
+
+
+def test_gpu_qbvh_build_layout_b():
+    """vx_b200_build_qbvh (layout B): the GPU-built quantized BVH4 + leaf-ordered triangles, downloaded, are valid
+    RT-unit input — every triangle in exactly one leaf, child boxes conservative under the RT unit's decode — and the reference's
+    traversal (port / compiled reference, through check_scene) finds on them what the GPU finds; distances equal those on the
+    host-built tree of the same mesh."""
+    import importlib
+    import os
+    from rtu_common import b_mesh, rtu, tracer_b
+    from test_gpu_rtu import check_scene
+    R = rtu()
+    host = importlib.import_module("vortex-raytracing_b200.host")
+    mesh = b_mesh(scenes.heightfield(40), two_materials=True)
+    n = mesh["tris"].shape[0]
+    hs = host.RtxHostScene([mesh])
+    karg = hs.setup(128, 96)
+    bufs = hs.buffers()
+    tr = tracer_b(bufs, karg, 1)
+    try:
+        hits_host = tr.trace_primary().copy()
+        used, box = tr.dev.build_qbvh(tr.bufs["tri"], n, tr.bufs["triEx"], tr.bufs["qbvh"])
+        assert n < used <= 2 * n
+        built = dict(bufs)
+        for name in ("tri", "triEx", "qbvh"):
+            arr = np.empty_like(bufs[name])
+            tr.bufs[name].copy_from_dev(arr)
+            built[name] = arr
+        built["bvh_nodes_used"] = used
+        hits_gpu = tr.trace_primary().copy()          # the rebuilt scene, straight from device memory
+    finally:
+        tr.close()
+    src = mesh["tris"].reshape(-1, 9).astype(np.float32)
+    out = built["tri"].view(np.float32).reshape(-1, 9)
+    assert sorted(map(bytes, src)) == sorted(map(bytes, out))                      # a permutation of the input
+    ex_src = bufs["triEx"].view(np.uint32).reshape(-1, 16)
+    ex_out = built["triEx"].view(np.uint32).reshape(-1, 16)
+    key = {bytes(t): bytes(e) for t, e in zip(bufs["tri"].view(np.float32).reshape(-1, 9), ex_src)}
+    assert all(key[bytes(t)] == bytes(e) for t, e in zip(out, ex_out))              # attributes moved with their triangles
+    assert np.array_equal(box[:3], src.reshape(-1, 3).min(axis=0)) and np.array_equal(box[3:], src.reshape(-1, 3).max(axis=0))
+    q = built["qbvh"].view(R.QNODE_DT)[:used]
+    assert (q["imask"] == 0).all()
+    leaves = q[q["leafIdx"] != 0]
+    assert len(leaves) == n and sorted(int(x) for x in leaves["leftFirst"]) == list(range(n))
+    tri = out.reshape(-1, 3, 3)
+    inner = np.nonzero(q["leafIdx"] == 0)[0]
+    seen = np.zeros(used, dtype=np.int32)
+    seen[0] = 1
+    for i in inner:                                                                 # every node: conservative child boxes
+        nd = q[i]
+        e = np.array([nd["ex"], nd["ey"], nd["ez"]], dtype=np.int32)
+        for k in range(4):
+            c = nd["children"][k]
+            if not c["meta"]:
+                continue
+            ci = int(nd["leftFirst"]) + k
+            seen[ci] += 1
+            lo = nd["origin"] + np.ldexp(c["q"][:3].astype(np.float32), e)
+            hi = nd["origin"] + np.ldexp(c["q"][3:].astype(np.float32), e)
+            child = q[ci]
+            if child["leafIdx"] != 0:
+                v = tri[child["leftFirst"]].reshape(-1, 3)
+                assert (v >= lo).all() and (v <= hi).all()
+            else:                                                                   # an inner child's own origin lies inside
+                assert (child["origin"] >= lo).all() and (child["origin"] <= hi).all()
+    assert (seen == 1).all()                                                        # a tree: every node referenced once
+    # same geometry, same arithmetic: the distances found on the GPU-built tree equal those on the host-built one
+    assert np.array_equal(hits_gpu["dist"], hits_host["dist"])
+    assert (hits_gpu["dist"] < 1e30).mean() > 0.1
+    check_scene(built, karg, 1)

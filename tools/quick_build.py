@@ -41,3 +41,36 @@ gpu_build_ms = tr.dev.stats()["kernel_ms"]
 gpu_ms = frame_ms()
 print(f"triangles={nt} host_build_s={host_s:.3f} gpu_build_ms={gpu_build_ms:.2f} primary_4k_frame_ms host_tree={host_ms:.3f} gpu_tree={gpu_ms:.3f}")
 tr.close()
+
+# ---- layout B: quantized BVH4 (vx_b200_build_qbvh) ----
+rtx = importlib.import_module("vortex-raytracing_b200.rtx_tracer")
+bm = {"tris": mesh["tris"], "triex": mesh["triex"], "texid": np.zeros(nt, np.uint32), "materials": [{"tex": mesh["tex"]}], "reflectivity": 0.0}
+t0 = time.perf_counter()
+hb = host.RtxHostScene([bm])
+c = np.float32(np.cos(np.pi / 4))
+hb.apply_transform(np.array([[1, 0, 0, 0], [0, c, c, 0], [0, -c, c, 0], [0, 0, 0, 1]], dtype=np.float32))
+kb = hb.setup(w, h)
+bb = hb.buffers()
+host_b_s = time.perf_counter() - t0
+tb = rtx.RtxTracer(w, h, 1, 1).init(bb)
+tb.setup({k: kb[k][0] for k in kb.dtype.names}, camera=rtx.CAMERA_PINHOLE)
+tb._upload_args()
+
+
+def frame_b_ms():
+    ms = []
+    for i in range(6):
+        tb.launch()
+        if i >= 2:
+            ms.append(tb.dev.last_kernel_ms())
+    return float(np.mean(ms))
+
+
+host_b_ms = frame_b_ms()
+tb.dev.build_qbvh(tb.bufs["tri"], nt, tb.bufs["triEx"], tb.bufs["qbvh"])
+used, _ = tb.dev.build_qbvh(tb.bufs["tri"], nt, tb.bufs["triEx"], tb.bufs["qbvh"])
+gpu_b_build_ms = tb.dev.stats()["kernel_ms"]
+gpu_b_ms = frame_b_ms()
+print(f"layout B: triangles={nt} host_build_s={host_b_s:.3f} (nodes {bb['bvh_nodes_used']}) gpu_build_ms={gpu_b_build_ms:.2f} (nodes {used}) "
+      f"primary_4k_frame_ms host_tree={host_b_ms:.3f} gpu_tree={gpu_b_ms:.3f}")
+tb.close()

@@ -14,6 +14,7 @@
 // with one atomic counter per internal node, then a relabelling pass that lays the children of internal node i at slots
 // 1+2i and 2+2i so the reference's "children are adjacent" addressing holds.  One-triangle leaves.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cfloat>
 #include <cstdint>
 #include "rt_layouts.h"
@@ -200,61 +201,271 @@ cudaError_t alloc(T **p, size_t count) { return cudaMalloc(reinterpret_cast<void
 
 }  // namespace
 
-int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches) {
-  if (n == 0) return -(int)cudaErrorInvalidValue;
-  const float *tf = reinterpret_cast<const float *>(tri);
+namespace {
+// the radix tree of a mesh, on the device: Karras arrays + fitted boxes
+struct Lbvh {
   float *cb = nullptr;
   Box3 *leaf_box = nullptr, *int_box = nullptr;
   uint64_t *keys = nullptr, *keys2 = nullptr;
   uint32_t *vals = nullptr, *vals2 = nullptr, *parent_int = nullptr, *parent_leaf = nullptr, *arrived = nullptr;
   uint2 *children = nullptr;
   void *tmp = nullptr;
-  size_t tmp_bytes = 0;
-  cudaError_t e = cudaSuccess;
-  int nl = 0;
+  const uint32_t *order = nullptr;   // sorted position -> triangle (points into vals / vals2)
+  int launches = 0;
+  void release() {
+    cudaFree(cb), cudaFree(leaf_box), cudaFree(int_box), cudaFree(keys), cudaFree(keys2), cudaFree(vals), cudaFree(vals2);
+    cudaFree(parent_int), cudaFree(parent_leaf), cudaFree(arrived), cudaFree(children), cudaFree(tmp);
+  }
+};
+
 #define VXB_TRY(x)                     \
   do {                                 \
     if (e == cudaSuccess) e = (x);     \
   } while (0)
-  VXB_TRY(alloc(&cb, 6));
-  VXB_TRY(alloc(&leaf_box, n));
-  VXB_TRY(alloc(&int_box, n));
-  VXB_TRY(alloc(&keys, n));
-  VXB_TRY(alloc(&keys2, n));
-  VXB_TRY(alloc(&vals, n));
-  VXB_TRY(alloc(&vals2, n));
-  VXB_TRY(alloc(&parent_int, n));
-  VXB_TRY(alloc(&parent_leaf, n));
-  VXB_TRY(alloc(&arrived, n));
-  VXB_TRY(alloc(&children, n));
-  cub::DoubleBuffer<uint64_t> dk(keys, keys2);
-  cub::DoubleBuffer<uint32_t> dv(vals, vals2);
+
+cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t) {
+  size_t tmp_bytes = 0;
+  cudaError_t e = cudaSuccess;
+  VXB_TRY(alloc(&t.cb, 6));
+  VXB_TRY(alloc(&t.leaf_box, n));
+  VXB_TRY(alloc(&t.int_box, n));
+  VXB_TRY(alloc(&t.keys, n));
+  VXB_TRY(alloc(&t.keys2, n));
+  VXB_TRY(alloc(&t.vals, n));
+  VXB_TRY(alloc(&t.vals2, n));
+  VXB_TRY(alloc(&t.parent_int, n));
+  VXB_TRY(alloc(&t.parent_leaf, n));
+  VXB_TRY(alloc(&t.arrived, n));
+  VXB_TRY(alloc(&t.children, n));
+  cub::DoubleBuffer<uint64_t> dk(t.keys, t.keys2);
+  cub::DoubleBuffer<uint32_t> dv(t.vals, t.vals2);
   VXB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
-  VXB_TRY(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
-  if (e == cudaSuccess) {
-    const unsigned blocks = (n + 255) / 256;
-    k_init_bounds<<<1, 32, 0, stream>>>(cb);
-    k_leaf_boxes<<<blocks, 256, 0, stream>>>(tf, n, leaf_box, cb);
-    k_morton<<<blocks, 256, 0, stream>>>(tf, n, cb, keys, vals);
-    nl += 3;
-    VXB_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
-    nl += 1;   // counted as one library step (CUB launches several kernels)
-    VXB_TRY(cudaMemsetAsync(arrived, 0, (size_t)n * 4, stream));
-    if (n > 1) {
-      k_radix_tree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(dk.Current(), (int)n, children, parent_int, parent_leaf);
-      k_fit<<<blocks, 256, 0, stream>>>(children, parent_int, parent_leaf, dv.Current(), leaf_box, int_box, arrived, n);
-      nl += 2;
+  VXB_TRY(cudaMalloc(&t.tmp, tmp_bytes ? tmp_bytes : 16));
+  if (e != cudaSuccess) return e;
+  const unsigned blocks = (n + 255) / 256;
+  k_init_bounds<<<1, 32, 0, stream>>>(t.cb);
+  k_leaf_boxes<<<blocks, 256, 0, stream>>>(tf, n, t.leaf_box, t.cb);
+  k_morton<<<blocks, 256, 0, stream>>>(tf, n, t.cb, t.keys, t.vals);
+  t.launches += 3;
+  VXB_TRY(cub::DeviceRadixSort::SortPairs(t.tmp, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
+  t.launches += 1;   // counted as one library step (CUB launches several kernels)
+  VXB_TRY(cudaMemsetAsync(t.arrived, 0, (size_t)n * 4, stream));
+  t.order = dv.Current();
+  if (n > 1 && e == cudaSuccess) {
+    k_radix_tree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(dk.Current(), (int)n, t.children, t.parent_int, t.parent_leaf);
+    k_fit<<<blocks, 256, 0, stream>>>(t.children, t.parent_int, t.parent_leaf, t.order, t.leaf_box, t.int_box, t.arrived, n);
+    t.launches += 2;
+  }
+  VXB_TRY(cudaGetLastError());
+  return e;
+}
+
+// ------------------------------------------------------------------------------------------------ layout B emission
+// BVH2 -> BVH4: the internal nodes at even depth survive, each adopting its grandchildren (a leaf child stays one slot);
+// every triangle is a one-triangle leaf node.  Children of a surviving node are consecutive, as the RT unit addresses them
+// (calcNodePtr(base, leftFirst + k), sim/simx/rt_traversal.cpp:69-75).
+__global__ void k_b_parity(const uint32_t *__restrict__ parent_int, uint32_t n_int, uint8_t *__restrict__ even) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_int) return;
+  uint32_t d = 0;
+  for (uint32_t c = i; parent_int[c] != 0xFFFFFFFFu; c = parent_int[c]) ++d;
+  even[i] = (d & 1u) ? 0 : 1;
+}
+__global__ void k_b_count(const uint2 *__restrict__ children, const uint8_t *__restrict__ even, uint32_t n_int, uint32_t *__restrict__ nchild) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_int) return;
+  uint32_t c = 0;
+  if (even[i]) {
+    uint2 ch = children[i];
+    c = ((ch.x & kLeafBit) ? 1u : 2u) + ((ch.y & kLeafBit) ? 1u : 2u);
+  }
+  nchild[i] = c;
+}
+// the (up to four) children of surviving node i, in slot order
+__device__ __forceinline__ uint32_t b_children(const uint2 *__restrict__ children, uint32_t i, uint32_t out[4]) {
+  uint2 ch = children[i];
+  uint32_t cc[2] = {ch.x, ch.y}, k = 0;
+#pragma unroll
+  for (int s = 0; s < 2; ++s) {
+    if (cc[s] & kLeafBit) {
+      out[k++] = cc[s];
+    } else {
+      uint2 g = children[cc[s]];
+      out[k++] = g.x, out[k++] = g.y;
     }
-    k_emit<<<blocks, 256, 0, stream>>>(children, dv.Current(), leaf_box, int_box, n, nodes, triIdx, tri_first);
-    nl += 1;
+  }
+  return k;
+}
+__global__ void k_b_assign(const uint2 *__restrict__ children, const uint8_t *__restrict__ even, const uint32_t *__restrict__ first,
+                           uint32_t n_int, uint32_t *__restrict__ idx_int, uint32_t *__restrict__ idx_leaf) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_int || !even[i]) return;
+  if (i == 0) idx_int[0] = 0;
+  uint32_t kids[4];
+  uint32_t nk = b_children(children, i, kids), base = 1u + first[i];
+  for (uint32_t k = 0; k < nk; ++k) {
+    if (kids[k] & kLeafBit) idx_leaf[kids[k] & ~kLeafBit] = base + k;
+    else idx_int[kids[k]] = base + k;
+  }
+}
+
+// quantization of one node (raytracing/bvh.cpp:200-258): origin = the node's own min corner, one power-of-two step per
+// axis, child corners floor/ceil'ed to 8 bits — and then widened until the box the RT unit decodes
+// (origin + ldexp(q, e), rt_traversal.cpp:61-67) really contains the child, as the host builder does.
+__device__ __forceinline__ int b_exponent(float extent) {
+  if (!(extent > 0.0f)) return 0;
+  float e = ceilf(log2f(extent / 255.0f));
+  return (int)fminf(fmaxf(e, -126.0f), 127.0f);
+}
+__device__ __forceinline__ bool b_quantize_axis(float origin, int e, float lo, float hi, uint8_t &qlo, uint8_t &qhi) {
+  float scale = ldexpf(1.0f, e);
+  float a = floorf((lo - origin) / scale), b = ceilf((hi - origin) / scale);
+  if (!(a >= 0.0f)) a = 0.0f;
+  if (!(b >= 0.0f)) b = 0.0f;
+  while (a > 0.0f && origin + ldexpf(a, e) > lo) a -= 1.0f;
+  while (b <= 255.0f && origin + ldexpf(b, e) < hi) b += 1.0f;
+  if (b > 255.0f || a > 255.0f) return false;
+  qlo = (uint8_t)a, qhi = (uint8_t)b;
+  return true;
+}
+__device__ void b_write_node(uint8_t *dst, const Box3 &self, const Box3 *kid, uint32_t nk, uint32_t leftFirst, uint32_t leafIdx) {
+  int e[3];
+  uint8_t q[4][6];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    e[a] = b_exponent(self.hi[a] - self.lo[a]);
+    for (;;) {
+      bool ok = true;
+      for (uint32_t k = 0; k < nk && ok; ++k) ok = b_quantize_axis(self.lo[a], e[a], kid[k].lo[a], kid[k].hi[a], q[k][a], q[k][3 + a]);
+      if (ok || e[a] == 127) break;
+      e[a]++;
+    }
+  }
+  uint32_t w[13];   // 52 bytes, the record is only 4-byte aligned
+  w[0] = __float_as_uint(self.lo[0]), w[1] = __float_as_uint(self.lo[1]), w[2] = __float_as_uint(self.lo[2]);
+  w[3] = (uint32_t)(uint8_t)(int8_t)e[0] | (uint32_t)(uint8_t)(int8_t)e[1] << 8 | (uint32_t)(uint8_t)(int8_t)e[2] << 16;   // imask 0 = BLAS node
+  w[4] = leftFirst, w[5] = leafIdx;
+  uint8_t cb[28];
+  for (uint32_t k = 0; k < 4; ++k) {
+    cb[7 * k] = k < nk ? 1 : 0;
+    for (int c = 0; c < 6; ++c) cb[7 * k + 1 + c] = k < nk ? q[k][c] : 0;
+  }
+  for (int i = 0; i < 7; ++i) w[6 + i] = (uint32_t)cb[4 * i] | (uint32_t)cb[4 * i + 1] << 8 | (uint32_t)cb[4 * i + 2] << 16 | (uint32_t)cb[4 * i + 3] << 24;
+  uint32_t *o = reinterpret_cast<uint32_t *>(dst);
+  for (int i = 0; i < 13; ++i) o[i] = w[i];
+}
+__global__ void k_b_emit_inner(const uint2 *__restrict__ children, const uint8_t *__restrict__ even, const uint32_t *__restrict__ first,
+                               const uint32_t *__restrict__ idx_int, const uint32_t *__restrict__ order, const Box3 *__restrict__ leaf_box,
+                               const Box3 *__restrict__ int_box, uint32_t n_int, uint8_t *__restrict__ qbvh) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_int || !even[i]) return;
+  uint32_t kids[4];
+  uint32_t nk = b_children(children, i, kids);
+  Box3 kb[4];
+  for (uint32_t k = 0; k < nk; ++k) kb[k] = (kids[k] & kLeafBit) ? leaf_box[order[kids[k] & ~kLeafBit]] : int_box[kids[k]];
+  b_write_node(qbvh + (size_t)idx_int[i] * sizeof(QNodeB), int_box[i], kb, nk, 1u + first[i], 0u);
+}
+// one-triangle leaves + the triangles and their attributes moved into leaf order (layout B has no index indirection)
+__global__ void k_b_emit_leaf(const uint32_t *__restrict__ idx_leaf, const uint32_t *__restrict__ order, const Box3 *__restrict__ leaf_box,
+                              uint32_t n, uint32_t tri_first, uint8_t *__restrict__ qbvh, const float *__restrict__ tri_in,
+                              float *__restrict__ tri_out, const uint4 *__restrict__ ex_in, uint4 *__restrict__ ex_out) {
+  uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= n) return;
+  uint32_t src = order[pos];
+  uint32_t node = n == 1 ? 0u : idx_leaf[pos];
+  b_write_node(qbvh + (size_t)node * sizeof(QNodeB), leaf_box[src], nullptr, 0, tri_first + pos, 1u);
+#pragma unroll
+  for (int k = 0; k < 9; ++k) tri_out[(size_t)pos * 9 + k] = tri_in[(size_t)src * 9 + k];
+  if (ex_in) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) ex_out[(size_t)pos * 4 + k] = ex_in[(size_t)src * 4 + k];
+  }
+}
+__global__ void k_b_root_box(const Box3 *__restrict__ leaf_box, const Box3 *__restrict__ int_box, const uint32_t *__restrict__ order,
+                             uint32_t n, float *__restrict__ out6) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const Box3 &b = n == 1 ? leaf_box[order[0]] : int_box[0];
+  for (int a = 0; a < 3; ++a) out6[a] = b.lo[a], out6[3 + a] = b.hi[a];
+}
+
+}  // namespace
+
+int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches) {
+  if (n == 0) return -(int)cudaErrorInvalidValue;
+  Lbvh t;
+  cudaError_t e = lbvh_tree(reinterpret_cast<const float *>(tri), n, stream, t);
+  if (e == cudaSuccess) {
+    k_emit<<<(n + 255) / 256, 256, 0, stream>>>(t.children, t.order, t.leaf_box, t.int_box, n, nodes, triIdx, tri_first);
+    t.launches += 1;
     VXB_TRY(cudaGetLastError());
     VXB_TRY(cudaStreamSynchronize(stream));
   }
-#undef VXB_TRY
-  cudaFree(cb), cudaFree(leaf_box), cudaFree(int_box), cudaFree(keys), cudaFree(keys2), cudaFree(vals), cudaFree(vals2);
-  cudaFree(parent_int), cudaFree(parent_leaf), cudaFree(arrived), cudaFree(children), cudaFree(tmp);
-  if (launches) *launches = nl;
+  t.release();
+  if (launches) *launches = t.launches;
   return e == cudaSuccess ? 0 : -(int)e;
 }
+
+int build_qbvh4(TriA *tri, TriExB *triEx, uint32_t n, uint32_t tri_first, QNodeB *qbvh, uint64_t qbvh_capacity, cudaStream_t stream,
+                uint32_t *nodes_used, float *root_box6, int *launches) {
+  if (n == 0) return -(int)cudaErrorInvalidValue;
+  Lbvh t;
+  const uint32_t n_int = n - 1;
+  uint8_t *even = nullptr;
+  uint32_t *nchild = nullptr, *first = nullptr, *idx_int = nullptr, *idx_leaf = nullptr;
+  float *tri_tmp = nullptr, *box_dev = nullptr;
+  uint4 *ex_tmp = nullptr;
+  void *scan_tmp = nullptr;
+  size_t scan_bytes = 0;
+  uint32_t total = 1;
+  cudaError_t e = lbvh_tree(reinterpret_cast<const float *>(tri), n, stream, t);
+  VXB_TRY(alloc(&even, n));
+  VXB_TRY(alloc(&nchild, n));
+  VXB_TRY(alloc(&first, n));
+  VXB_TRY(alloc(&idx_int, n));
+  VXB_TRY(alloc(&idx_leaf, n));
+  VXB_TRY(alloc(&tri_tmp, (size_t)n * 9));
+  VXB_TRY(alloc(&box_dev, 6));
+  if (triEx) VXB_TRY(alloc(&ex_tmp, (size_t)n * 4));
+  VXB_TRY(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, nchild, first, (int)(n_int ? n_int : 1), stream));
+  VXB_TRY(cudaMalloc(&scan_tmp, scan_bytes ? scan_bytes : 16));
+  if (e == cudaSuccess && n_int) {
+    const unsigned ib = (n_int + 255) / 256;
+    k_b_parity<<<ib, 256, 0, stream>>>(t.parent_int, n_int, even);
+    k_b_count<<<ib, 256, 0, stream>>>(t.children, even, n_int, nchild);
+    VXB_TRY(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, nchild, first, (int)n_int, stream));
+    t.launches += 3;
+    uint32_t last[2] = {0, 0};
+    VXB_TRY(cudaMemcpyAsync(&last[0], first + n_int - 1, 4, cudaMemcpyDeviceToHost, stream));
+    VXB_TRY(cudaMemcpyAsync(&last[1], nchild + n_int - 1, 4, cudaMemcpyDeviceToHost, stream));
+    VXB_TRY(cudaStreamSynchronize(stream));
+    total = 1 + last[0] + last[1];
+  }
+  if (e == cudaSuccess && total > qbvh_capacity) e = cudaErrorInvalidValue;   // caller's node buffer is too small
+  if (e == cudaSuccess) {
+    VXB_TRY(cudaMemcpyAsync(tri_tmp, tri, (size_t)n * 36, cudaMemcpyDeviceToDevice, stream));
+    if (triEx) VXB_TRY(cudaMemcpyAsync(ex_tmp, triEx, (size_t)n * 64, cudaMemcpyDeviceToDevice, stream));
+    if (n_int) {
+      const unsigned ib = (n_int + 255) / 256;
+      k_b_assign<<<ib, 256, 0, stream>>>(t.children, even, first, n_int, idx_int, idx_leaf);
+      k_b_emit_inner<<<ib, 256, 0, stream>>>(t.children, even, first, idx_int, t.order, t.leaf_box, t.int_box, n_int,
+                                             reinterpret_cast<uint8_t *>(qbvh));
+      t.launches += 2;
+    }
+    k_b_emit_leaf<<<(n + 255) / 256, 256, 0, stream>>>(idx_leaf, t.order, t.leaf_box, n, tri_first, reinterpret_cast<uint8_t *>(qbvh),
+                                                       tri_tmp, reinterpret_cast<float *>(tri), ex_tmp, reinterpret_cast<uint4 *>(triEx));
+    k_b_root_box<<<1, 32, 0, stream>>>(t.leaf_box, t.int_box, t.order, n, box_dev);
+    t.launches += 2;
+    VXB_TRY(cudaGetLastError());
+    if (root_box6) VXB_TRY(cudaMemcpyAsync(root_box6, box_dev, 24, cudaMemcpyDeviceToHost, stream));
+    VXB_TRY(cudaStreamSynchronize(stream));
+  }
+  t.release();
+  cudaFree(even), cudaFree(nchild), cudaFree(first), cudaFree(idx_int), cudaFree(idx_leaf), cudaFree(tri_tmp), cudaFree(box_dev);
+  cudaFree(ex_tmp), cudaFree(scan_tmp);
+  if (nodes_used) *nodes_used = total;
+  if (launches) *launches = t.launches;
+  return e == cudaSuccess ? 0 : -(int)e;
+}
+#undef VXB_TRY
 
 }  // namespace vxb

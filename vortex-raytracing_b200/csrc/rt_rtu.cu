@@ -623,12 +623,10 @@ int launch_program_t(const RtuRender &p, int num_sms, cudaStream_t stream) {
 // shader programs over the traceRay/getWork/getAttr/commit shim (vx_raytrace_b200.cuh); `program` indexes rt_rtu_programs.cuh
 int launch_rtu_program(const RtuRender &p, uint32_t program, int num_sms, cudaStream_t stream) {
   // the closest-hit shader recurses through the SBT for mirror rays: give the device stack room for kMaxBounce frames
-  static bool stack_set = false;
-  if (!stack_set) {
-    size_t cur = 0;
-    cudaDeviceGetLimit(&cur, cudaLimitStackSize);
-    if (cur < 12288) cudaDeviceSetLimit(cudaLimitStackSize, 12288);
-    stack_set = true;
+  size_t cur = 0;   // per device, so queried at every launch (a host call, microseconds)
+  if (cudaDeviceGetLimit(&cur, cudaLimitStackSize) != cudaSuccess || cur < 12288) {
+    cudaError_t e = cudaDeviceSetLimit(cudaLimitStackSize, 12288);
+    if (e != cudaSuccess) return -(int)e;
   }
   switch (program) {
     case 0: return launch_program_t<ShaderSet<false>>(p, num_sms, stream);

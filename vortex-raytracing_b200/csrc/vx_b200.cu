@@ -413,6 +413,44 @@ public:
     if (nodes_used) *nodes_used = 2 * tri_count - 1;
     return 0;
   }
+  int build_qbvh(uint64_t tri_addr, uint64_t tri_count, uint64_t tri_first, uint64_t ex_addr, uint64_t qbvh_addr, uint64_t capacity,
+                 uint64_t *nodes_used, float *root_box6) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    if (tri_count == 0 || tri_count > 0x7FFFFFFFull) return fail("vx_b200_build_qbvh: bad triangle count");
+    if (run_pending_) {
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+    }
+    TriA *tri = nullptr;
+    TriExB *ex = nullptr;
+    QNodeB *q = nullptr;
+    if (resolve(tri_addr, tri_count * sizeof(TriA), 4, "tri", &tri)) return -1;
+    if (ex_addr != ~0ull && resolve(ex_addr, tri_count * sizeof(TriExB), 4, "triEx", &ex)) return -1;
+    if (resolve(qbvh_addr, capacity * sizeof(QNodeB), 4, "qbvh", &q)) return -1;
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    cudaEventRecord(e0, stream_);
+    int nl = 0;
+    uint32_t used = 0;
+    int rc = build_qbvh4(tri, ex, (uint32_t)tri_count, (uint32_t)tri_first, q, capacity, stream_, &used, root_box6, &nl);
+    cudaEventRecord(e1, stream_);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0), cudaEventDestroy(e1);
+    if (rc != 0) return fail("vx_b200_build_qbvh: %s (capacity %llu nodes, needed %u)", cudaGetErrorString((cudaError_t)(-rc)),
+                             (unsigned long long)capacity, used);
+    uint64_t start = 0;   // the buffers changed under the caches keyed on upload generations
+    if (auto *b = space_.find(tri_addr, 1, &start)) b->write_gen = ++generation_;
+    if (ex_addr != ~0ull)
+      if (auto *b = space_.find(ex_addr, 1, &start)) b->write_gen = ++generation_;
+    if (auto *b = space_.find(qbvh_addr, 1, &start)) b->write_gen = ++generation_;
+    stats_.kernel_launches = (uint64_t)nl, stats_.prep_launches = 0, stats_.kernel_ms = ms, stats_.prep_ms = 0;
+    if (nodes_used) *nodes_used = used;
+    return 0;
+  }
   int set_remote_framebuffer(const void *handle, uint64_t offset, uint64_t bytes) {
     std::lock_guard<std::mutex> g(mu_);
     CUDA_TRY(cudaSetDevice(cuda_dev_));
@@ -1161,6 +1199,18 @@ VXB_EXPORT int vx_b200_build_bvh(vx_device_h h, vx_buffer_h htri, uint64_t tri_f
     return fail("vx_b200_build_bvh: range outside a buffer");
   return ((Device *)h)->build_bvh(t->addr + tri_first * sizeof(vxb::TriA), tri_count, tri_first, b->addr + node_first * sizeof(vxb::BvhNodeA),
                                   i->addr + slot_first * 4, nodes_used);
+}
+VXB_EXPORT int vx_b200_build_qbvh(vx_device_h h, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h htriEx,
+                                  vx_buffer_h hqbvh, uint64_t node_first, uint64_t *nodes_used, float *root_box6) {
+  if (!h || !htri || !hqbvh) return -1;
+  auto t = (Buffer *)htri, q = (Buffer *)hqbvh, x = (Buffer *)htriEx;
+  if ((tri_first + tri_count) * sizeof(vxb::TriA) > t->size || (x && (tri_first + tri_count) * sizeof(vxb::TriExB) > x->size) ||
+      node_first * sizeof(vxb::QNodeB) >= q->size)
+    return fail("vx_b200_build_qbvh: range outside a buffer");
+  uint64_t capacity = q->size / sizeof(vxb::QNodeB) - node_first;
+  return ((Device *)h)->build_qbvh(t->addr + tri_first * sizeof(vxb::TriA), tri_count, tri_first,
+                                   x ? x->addr + tri_first * sizeof(vxb::TriExB) : ~0ull, q->addr + node_first * sizeof(vxb::QNodeB), capacity,
+                                   nodes_used, root_box6);
 }
 VXB_EXPORT int vx_b200_export_buffer(vx_buffer_h hbuffer, void *ipc_handle_64, uint64_t *offset) {
   if (!hbuffer || !ipc_handle_64 || !offset) return -1;

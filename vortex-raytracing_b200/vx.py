@@ -24,7 +24,7 @@ EXPORTS = (
     "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
-    "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_stream vx_b200_last_kernel_ms "
     "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_trace_rays_host vx_b200_last_error"
 ).split()
 
@@ -67,6 +67,7 @@ def lib():
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
             "vx_b200_trace_rays_host": [H, B, C.c_void_p, u64, C.c_void_p],
             "vx_b200_build_bvh": [H, B, u64, u64, B, u64, B, u64, C.POINTER(u64)],
+            "vx_b200_build_qbvh": [H, B, u64, u64, B, B, u64, C.POINTER(u64), C.POINTER(C.c_float)],
             "vx_b200_export_buffer": [B, vp, C.POINTER(u64)], "vx_b200_set_remote_framebuffer": [H, vp, u64, u64],
         }
         for name, args in sig.items():
@@ -215,6 +216,15 @@ class Device:
         _check(lib().vx_b200_build_bvh(self.h, tri.h, tri_first, tri_count, bvh.h, node_first, tri_idx.h, slot_first, C.byref(used)),
                "vx_b200_build_bvh")
         return used.value
+
+    def build_qbvh(self, tri, tri_count, tri_ex, qbvh, tri_first=0, node_first=0):
+        """GPU build of the layout-B quantized BVH4 of triangles [tri_first, tri_first+tri_count); `tri` / `tri_ex` are permuted
+        in place into leaf order.  Returns (nodes written, root box as 6 floats)."""
+        used = C.c_uint64()
+        box = (C.c_float * 6)()
+        _check(lib().vx_b200_build_qbvh(self.h, tri.h, tri_first, tri_count, tri_ex.h if tri_ex is not None else None, qbvh.h,
+                                        node_first, C.byref(used), box), "vx_b200_build_qbvh")
+        return used.value, np.array(list(box), dtype=np.float32)
 
     def set_remote_framebuffer(self, handle, offset=0, nbytes=0):
         """handle: the 64 bytes of Buffer.ipc_export() from the image owner's process (None detaches)"""
