@@ -362,9 +362,11 @@ def run_b200(args, wl, name):
     if rank == 0 and world == 1 and args.extra:
         tr.close()
         tr = None
-        for other in ("primary_4k_1m", "cfg2_4k_diffuse4_1m"):
+        for other in ("primary_4k_1m", "cfg2_4k_diffuse4_1m", "cfg3_8k_primary+shadow_1m"):
             if other != name:
                 extra[other] = quick_run(other, local, kernel=args.kernel)
+        if "cfg3_8k_primary+shadow_1m" in extra:   # --gpus N > 1 runs BASELINE configs[3] (strong scaling); this is its one-GPU point
+            extra["cfg3_8k_primary+shadow_1m"]["note"] += "; the one-GPU base of the strong-scaling series that --gpus 2/4/8 measure"
         extra["rtu_1080p_primary_100k"] = quick_run_rtu(local, with_cpu=not args.no_cpu)
 
     cpu = None

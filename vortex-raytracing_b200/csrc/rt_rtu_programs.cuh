@@ -11,6 +11,10 @@
 //                       of odd index (a cut-out): exercises the path the shipped any-hit never takes.
 #pragma once
 
+#ifndef VXB_PROGRAM_MIN_BLOCKS
+#define VXB_PROGRAM_MIN_BLOCKS 3
+#endif
+
 struct RayPayload {     // shaders/shader.h:7-12
   f3 color;
   uint32_t bounce;
@@ -99,7 +103,7 @@ __device__ void sbt_call(RT &rt, uint32_t work, const KernelArgB &arg) {
 // kernel.cpp:41-133 with one lane in both roles (producer: traceRay per pixel; consumer: getWork + SBT dispatch until the
 // pixel's payload is done), on the tile scheduler of k_rtu_render.
 template <class P, bool STRICT, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads) k_rtu_program(const __grid_constant__ RtuRender p) {
+__global__ void __launch_bounds__(kBlockThreads, VXB_PROGRAM_MIN_BLOCKS) k_rtu_program(const __grid_constant__ RtuRender p) {
   uint32_t stk_e[STRICT ? 1 : kStackB];
   float stk_d[STRICT ? 1 : kStackB];
   const KernelArgB &a = p.arg;
