@@ -94,6 +94,7 @@ public:
     if (getenv("VORTEX_B200_MODE")) dcrs_[VX_DCR_B200_RT_MODE] = (uint32_t)env_u64("VORTEX_B200_MODE", 0);
     if (getenv("VORTEX_B200_ORDER")) dcrs_[VX_DCR_B200_RT_ORDER] = (uint32_t)env_u64("VORTEX_B200_ORDER", 0);
     if (getenv("VORTEX_B200_KERNEL")) dcrs_[VX_DCR_B200_RT_KERNEL] = (uint32_t)env_u64("VORTEX_B200_KERNEL", 0);
+    if (getenv("VORTEX_B200_CAMERA")) dcrs_[VX_DCR_B200_RT_CAMERA] = (uint32_t)env_u64("VORTEX_B200_CAMERA", 0);
     CUDA_TRY(cudaStreamSynchronize(stream_));
     return 0;
   }
