@@ -117,6 +117,28 @@ def test_incoherent_and_edge_rays(oracle):
             got = tr.trace_rays_host(rays)
             assert got.tobytes() == want.tobytes(), chunk
             assert tr.dev.stats()["rays"] == len(rays)
+        # coherence ordering of large batches (probe + octant/Morton sort + index array): same records at the same positions
+        base_launches = tr.dev.stats()["kernel_launches"]
+        os.environ["VORTEX_B200_RAY_ORDER_MIN"] = "1000"
+        os.environ["VORTEX_B200_RAY_ORDER"] = "1"                 # opt-in (device-side ordering costs more than it gains)
+        try:
+            for bits in ("7", "3", "9"):
+                os.environ["VORTEX_B200_RAY_ORDER_BITS"] = bits
+                assert tr.trace_rays(rays).tobytes() == want.tobytes(), bits
+            assert tr.dev.stats()["kernel_launches"] == 3            # keys + sort + trace: the random batch was reordered
+            scan = np.zeros((4096, 6), np.float32)                   # a coherent batch (one scanline of parallel rays) is not
+            scan[:, 0] = np.linspace(-1, 1, 4096)
+            scan[:, 1], scan[:, 5] = 0.3, 1.0
+            scan[:, 2] = -3.0
+            tr.trace_rays(scan)
+            assert tr.dev.stats()["kernel_launches"] == 2            # keys + trace
+            os.environ["VORTEX_B200_RAY_ORDER"] = "0"
+            assert tr.trace_rays(rays).tobytes() == want.tobytes()
+            assert tr.dev.stats()["kernel_launches"] == 1
+        finally:
+            for k in ("VORTEX_B200_RAY_ORDER_MIN", "VORTEX_B200_RAY_ORDER_BITS", "VORTEX_B200_RAY_ORDER"):
+                os.environ.pop(k, None)
+        assert base_launches >= 1
         assert tr.trace_rays_host(rays[:1]).tobytes() == want[:1].tobytes()
         assert len(tr.trace_rays_host(rays[:0])) == 0
         import torch

@@ -14,6 +14,7 @@
 // hold only the traversal state.  Per-ray arithmetic is unchanged from rt_raycast.cu — same slab and Moller-Trumbore
 // expressions, same shading expressions, -fmad=false — so strict order stays bit-identical to the reference
 // (tests/regression/raycast/render.h:74-276) and fast order differs from it only in equal-t ties.
+#include <cub/device/device_radix_sort.cuh>
 #include "rt_device.cuh"
 
 namespace vxb {
@@ -506,8 +507,9 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
         uint32_t item = chunk_next + my_rank;
         if (MODE == kModeTrace) {
           if (item < p.count) {
-            sm.u(C_PIX) = item;
-            begin_trace(L, sm, p, item, lc);
+            const uint32_t src = p.perm ? __ldg(p.perm + item) : item;   // coherence-ordered batch: item k is ray perm[k]
+            sm.u(C_PIX) = src;
+            begin_trace(L, sm, p, src, lc);
           }
         } else {
         uint32_t tile = item >> 5, in_tile = item & 31u;
@@ -556,6 +558,68 @@ int launch_mm(const RenderA &p, int num_sms, cudaStream_t stream) {
 }
 
 }  // namespace
+
+// ---------------------------------------------------------------- coherence ordering of ray batches
+namespace {
+__device__ __forceinline__ uint32_t spread10(uint32_t v) {   // 10 bits -> every third bit
+  v &= 0x3FFu;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+__global__ void k_ray_keys(const TlasNodeA *__restrict__ tlas, uint32_t root, const float *__restrict__ rays, uint32_t n, uint32_t bits,
+                           uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, uint32_t *__restrict__ jumps) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const float *r = reinterpret_cast<const float *>(tlas + root);   // aabbMin.xyz, leftRight, aabbMax.xyz, blas
+  float lo[3] = {__ldg(r), __ldg(r + 1), __ldg(r + 2)}, hi[3] = {__ldg(r + 4), __ldg(r + 5), __ldg(r + 6)};
+  uint32_t key = 0;
+  if (i < n) {
+    const float *q = rays + 6ull * i;
+    uint32_t c[3];
+    const float cells = (float)(1u << bits);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      float ext = hi[a] - lo[a];
+      float u = ext > 0.0f ? (__ldg(q + a) - lo[a]) / ext : 0.0f;
+      u = fminf(fmaxf(u, 0.0f), 1.0f);          // origins outside the scene fall into the border cells (NaN -> 0)
+      c[a] = min((uint32_t)(u * cells), (1u << bits) - 1u);
+    }
+    uint32_t morton = (spread10(c[0]) << 2) | (spread10(c[1]) << 1) | spread10(c[2]);
+    uint32_t octant = (__ldg(q + 3) < 0.0f ? 4u : 0u) | (__ldg(q + 4) < 0.0f ? 2u : 0u) | (__ldg(q + 5) < 0.0f ? 1u : 0u);
+    key = (octant << (3 * bits)) | morton;
+    keys[i] = key, idx[i] = i;
+  }
+  // incoherence probe: neighbours in different coarse cells (octant + the top two Morton bits per axis)
+  const uint32_t coarse = key >> (3 * bits >= 6 ? 3 * bits - 6 : 0);
+  uint32_t next = __shfl_down_sync(0xffffffffu, coarse, 1);
+  bool jump = (threadIdx.x & 31u) != 31u && i + 1 < n && next != coarse;
+  unsigned m = __ballot_sync(0xffffffffu, jump);
+  // one block in eight reports (a single counter: every warp reporting serialises 2^18 atomics per 2^23 rays)
+  if ((blockIdx.x & 7u) == 0 && (threadIdx.x & 31u) == 0 && m) atomicAdd(jumps, (uint32_t)__popc(m));
+}
+}  // namespace
+
+size_t ray_order_tmp_bytes(uint64_t n) {
+  size_t bytes = 0;
+  cub::DoubleBuffer<uint32_t> k(nullptr, nullptr), v(nullptr, nullptr);
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, (int)n, 0, 32);
+  return bytes;
+}
+cudaError_t ray_order_keys(const SceneA &scene, const float *rays, uint64_t n, uint32_t bits, const RayOrderBuffers &b, cudaStream_t stream) {
+  cudaError_t e = cudaMemsetAsync(b.jumps, 0, 4, stream);
+  if (e != cudaSuccess) return e;
+  k_ray_keys<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(scene.tlas, scene.tlas_root, rays, (uint32_t)n, bits, b.keys[0], b.idx[0], b.jumps);
+  return cudaGetLastError();
+}
+cudaError_t ray_order_sort(uint64_t n, uint32_t bits, const RayOrderBuffers &b, const uint32_t **sorted_idx, cudaStream_t stream) {
+  cub::DoubleBuffer<uint32_t> k(b.keys[0], b.keys[1]), v(b.idx[0], b.idx[1]);
+  size_t bytes = b.tmp_bytes;
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(b.tmp, bytes, k, v, (int)n, 0, (int)(3 * bits + 3), stream);
+  *sorted_idx = v.Current();
+  return e;
+}
 
 int launch_trace_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
   if (p.count == 0) return 0;

@@ -58,6 +58,7 @@ struct RenderA {
   const float *rays;        // 6 floats per ray, or nullptr => primary rays of `arg`
   HitA *hits;
   uint64_t count;
+  const uint32_t *perm;     // hit-record mode: work item k traces ray perm[k] (launch_ray_order), or nullptr = identity
 };
 
 struct TraceA {
@@ -84,6 +85,20 @@ int launch_trace_a(const TraceA &p, int num_sms, cudaStream_t stream);
 // the warp-scheduled ray state machine (rt_machine.cu); scenes must have < 2^27 BVH nodes (else use launch_render_a)
 int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream);
 // same machine, work items = rays p.rays[0..count) (or primary rays), output = p.hits; count < 2^32
+// Coherence ordering of caller-supplied rays (hit-record mode): keys = (direction octant, Morton code of the origin inside the
+// scene's bounds, `bits` per axis).  ray_order_keys fills keys/idx (idx = identity) and counts in *jumps how often neighbouring
+// rays fall into different coarse cells (a measure of how incoherent the batch already is); ray_order_sort sorts idx by key
+// (CUB radix sort over 3*bits+3 bits; tmp sized by ray_order_tmp_bytes).  Returns cudaError_t.
+struct RayOrderBuffers {
+  uint32_t *keys[2];
+  uint32_t *idx[2];
+  void *tmp;
+  size_t tmp_bytes;
+  uint32_t *jumps;   // device word
+};
+size_t ray_order_tmp_bytes(uint64_t n);
+cudaError_t ray_order_keys(const SceneA &scene, const float *rays, uint64_t n, uint32_t bits, const RayOrderBuffers &b, cudaStream_t stream);
+cudaError_t ray_order_sort(uint64_t n, uint32_t bits, const RayOrderBuffers &b, const uint32_t **sorted_idx, cudaStream_t stream);
 int launch_trace_machine(const RenderA &p, int num_sms, cudaStream_t stream);
 constexpr uint64_t kMachineMaxNodes = 1ull << 27;
 

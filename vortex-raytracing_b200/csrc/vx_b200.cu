@@ -113,6 +113,7 @@ public:
     if (rtu_tri_) cudaFree(rtu_tri_);
     pipe_free_locked();
     alt_free_locked();
+    ray_order_free_locked();
     if (counters_) cudaFree(counters_);
     if (tile_counter_) cudaFree(tile_counter_);
     if (h_counters_) cudaFreeHost(h_counters_);
@@ -702,6 +703,28 @@ private:
         if (p.quorum_refill < 2 || p.quorum_refill > 32) p.quorum_refill = 16;
         if (p.quorum_inner < 1 || p.quorum_inner >= p.quorum_refill) p.quorum_inner = p.quorum_refill / 2;
         p.rays = rays, p.hits = hits, p.count = count;
+        // Coherence ordering of large caller-supplied batches (opt-in, VORTEX_B200_RAY_ORDER=1): a probe counts how often
+        // neighbouring rays fall into different coarse cells; an incoherent batch is traced in (direction octant, origin Morton)
+        // order through an index array (results land at the rays' own positions).  Measured on BASELINE configs[4]
+        // (profiles/r01_sweep_ray_order.txt): rays that ARRIVE in that order trace 34 % faster (2.37 -> 1.77 ms), but ordering
+        // them here costs keys 0.05 + sort 0.27 ms and the indexed kernel runs 2.12 ms, so the call gets slower (2.66 vs
+        // 2.38 ms) — hence off by default; callers that can generate rays in a coherent order should.
+        if (rays && !pipe_hits_ && count >= env_u64("VORTEX_B200_RAY_ORDER_MIN", 1ull << 18) && env_u64("VORTEX_B200_RAY_ORDER", 0) != 0) {
+          uint32_t bits = (uint32_t)env_u64("VORTEX_B200_RAY_ORDER_BITS", 7);
+          if (bits < 2 || bits > 9) bits = 7;
+          if (ray_order_reserve_locked(count) != 0) return -1;
+          CUDA_TRY(ray_order_keys(sc, rays, count, bits, order_, stream_));
+          uint32_t jumps = 0;
+          CUDA_TRY(cudaMemcpyAsync(&jumps, order_.jumps, 4, cudaMemcpyDeviceToHost, stream_));
+          CUDA_TRY(cudaStreamSynchronize(stream_));
+          launches_ += 1;
+          if ((double)jumps * 8.0 > 0.25 * (double)count) {   // the probe samples one block in eight
+            const uint32_t *sorted = nullptr;
+            CUDA_TRY(ray_order_sort(count, bits, order_, &sorted, stream_));
+            launches_ += 1;   // the CUB sort counted as one library step
+            p.perm = sorted;
+          }
+        }
         // chunk of the host pipeline: kRunCtxs kernels share the SMs, so that one chunk's tail (its slowest rays) runs
         // under the other chunks' bodies instead of idling the device
         if (pipe_hits_) p.blocks_per_sm_cap = (uint32_t)env_u64("VORTEX_B200_HOST_BLOCKS_PER_SM", 2);
@@ -899,6 +922,33 @@ private:
       if (x.ev_end) cudaEventDestroy(x.ev_end);
       x = RunCtx{};
     }
+  }
+
+  // coherence ordering scratch (grow-only)
+  RayOrderBuffers order_{};
+  uint64_t order_cap_ = 0;
+  int ray_order_reserve_locked(uint64_t n) {
+    if (order_cap_ >= n) return 0;
+    ray_order_free_locked();
+    for (int i = 0; i < 2; i++) {
+      CUDA_TRY(cudaMalloc(&order_.keys[i], n * 4));
+      CUDA_TRY(cudaMalloc(&order_.idx[i], n * 4));
+    }
+    order_.tmp_bytes = ray_order_tmp_bytes(n);
+    CUDA_TRY(cudaMalloc(&order_.tmp, order_.tmp_bytes ? order_.tmp_bytes : 16));
+    CUDA_TRY(cudaMalloc(&order_.jumps, 4));
+    order_cap_ = n;
+    return 0;
+  }
+  void ray_order_free_locked() {
+    for (int i = 0; i < 2; i++) {
+      if (order_.keys[i]) cudaFree(order_.keys[i]);
+      if (order_.idx[i]) cudaFree(order_.idx[i]);
+    }
+    if (order_.tmp) cudaFree(order_.tmp);
+    if (order_.jumps) cudaFree(order_.jumps);
+    order_ = RayOrderBuffers{};
+    order_cap_ = 0;
   }
 
   std::mutex mu_;
