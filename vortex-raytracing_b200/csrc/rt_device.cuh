@@ -26,6 +26,16 @@ struct Local {   // per-thread work counters
   uint32_t lane_steps, warp_steps;   // traversal iterations of this lane / issued by this lane as its warp's leader
 };
 
+// k-th tile handed out by the work counter -> tile of the image and its cost group (0xFFFFFFFF = none)
+__device__ __forceinline__ uint32_t sched_tile(const TileSchedule &s, uint32_t k, uint32_t ntiles, uint32_t &group) {
+  group = 0xFFFFFFFFu;
+  if (!s.order) return k;
+  if (k < s.lead) return ntiles - s.lead + k;
+  const uint32_t q = k - s.lead, pos = q >> s.group_shift;
+  group = __ldg(s.order + pos);
+  return (group << s.group_shift) | (q & ((1u << s.group_shift) - 1u));
+}
+
 // One traversal iteration (a node fetch + its box tests, or one leaf) is about to run on the lanes converged here.
 // lane_steps / (32 * warp_steps) is the SIMT efficiency the simulator reports per RT unit (sim/simx/rt_unit.h:15-45,
 // rt_total_simt_efficiency / rt_total_warps).
@@ -39,6 +49,13 @@ __device__ __forceinline__ void simt_step(Local &lc) {
 }
 
 __device__ __forceinline__ float4 ldg4(const void *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
+// the same load pinned where it is written: the compiler otherwise sinks a node's box loads behind the branch on its header
+// word, which turns one round trip per node into two dependent ones (measured on the layout-B walk)
+__device__ __forceinline__ float4 ldg4_pinned(const void *p) {
+  float4 v;
+  asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 
 // ---- ray_t::intersect(aabbMin, aabbMax) (geometry.h:1447-1468) with the reciprocal hoisted ----
 // `nan_safe` is set for rays with an infinite reciprocal (a zero/denormal direction component): only then can

@@ -41,6 +41,7 @@ constexpr uint32_t F_ANY = 4, F_NAN = 8, F_INBLAS = 16, F_OCCL = 32;
 enum : uint32_t {
   C_PIX, C_COLX, C_COLY, C_COLZ, C_RADX, C_RADY, C_RADZ, C_THRX, C_THRY, C_THRZ, C_SEED, C_PACK,   // PACK: bounce | sample<<8 | stage<<31
   C_WOX, C_WOY, C_WOZ, C_WDX, C_WDY, C_WDZ,                                                         // world-space ray of the slot
+  C_T0, C_GRP,                                                                                      // schedule feedback: clock at GEN, cost group
   C_BASE_END,
   C_TEXX = C_BASE_END, C_TEXY, C_TEXZ, C_ATT, C_NDL, C_NX, C_NY, C_NZ, C_IX, C_IY, C_IZ, C_REFL, C_PDX, C_PDY, C_PDZ,   // shadow continuation
   C_SHADOW_END
@@ -274,7 +275,7 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
 __device__ __forceinline__ bool is_inner(const Lane &L) { return (L.st & S_MASK) == S_TRAV && (L.cur >> kKindShift) == 0u; }
 
 // TRAV: runs until fewer than `quorum` lanes of the warp are still traversing
-template <bool STRICT, bool STATS>
+template <bool STRICT, bool STATS, bool COST>
 __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &sc, uint32_t quorum, uint32_t inner_quorum, uint32_t *stk_e,
                                          float *stk_d, Local &lc) {
   for (;;) {
@@ -286,12 +287,14 @@ __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &
       if ((uint32_t)__popc(m) < inner_quorum) break;
       if (inner) {
         simt_step<STATS>(lc);
+        if (COST) sm.u(C_T0) += 1u;
         if (STRICT) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);   // the reference's own BVH2 walk
         else step_wide<STATS>(L, careful, stk_e, stk_d, lc);                        // 4-wide records (the launch guarantees sc.wide)
       }
     }
     if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) {
       simt_step<STATS>(lc);
+      if (COST) sm.u(C_T0) += 1u;
       step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
     }
     unsigned t = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
@@ -337,7 +340,7 @@ __device__ __forceinline__ void begin_trace(Lane &L, const Smem &sm, const Rende
 
 // POST: closest-hit shading / shadow resolution and the bounce loop of Trace (render.h:210-276) and of the extended
 // modes (shadow rays, diffuse bounces; same expressions as rt_raycast.cu:trace_ext and the CPU oracles' TraceExt)
-template <uint32_t MODE, bool STATS>
+template <uint32_t MODE, bool STATS, bool COST>
 __device__ __forceinline__ void post(Lane &L, const Smem &sm, const RenderA &p, Local &lc) {
   constexpr bool SHADOW = (MODE & 1u) != 0, DIFFUSE = (MODE & 2u) != 0;
   const KernelArgA &a = p.arg;
@@ -440,10 +443,13 @@ __device__ __forceinline__ void post(Lane &L, const Smem &sm, const RenderA &p, 
     return;
   }
   p.out[pix] = rgb32f_to_rgb8(color);
+  // most traversal steps spent on one pixel of this group (one pixel in eight reports; a reduction without return value, so
+  // the warp does not wait for it)
+  if (COST && sm.u(C_GRP) != 0xFFFFFFFFu) atomicMax(p.sched.cost + sm.u(C_GRP), sm.u(C_T0));
   L.st = S_EMPTY;
 }
 
-template <uint32_t MODE, bool STRICT, bool STATS>
+template <uint32_t MODE, bool STRICT, bool STATS, bool COST>
 __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(const __grid_constant__ RenderA p) {
   constexpr uint32_t kCols = (MODE == kModeTrace) ? C_BASE_END : ((MODE & 1u) ? C_SHADOW_END : C_BASE_END);
   __shared__ float s_cols[kCols * kBlockThreads];
@@ -474,11 +480,11 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
     unsigned done = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_DONE);
     const uint32_t quorum = exhausted ? 1u : p.quorum_refill;
     if (trav && ((uint32_t)__popc(trav) >= quorum || (!done && exhausted))) {
-      traverse<STRICT, STATS>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk_e, stk_d, lc);
+      traverse<STRICT, STATS, COST>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk_e, stk_d, lc);
       continue;
     }
     if (done) {
-      if ((L.st & S_MASK) == S_DONE) post<MODE, STATS>(L, sm, p, lc);
+      if ((L.st & S_MASK) == S_DONE) post<MODE, STATS, COST>(L, sm, p, lc);
       continue;   // POST may have queued follow-up rays; re-evaluate before pulling new pixels
     }
     if (exhausted) {
@@ -512,7 +518,8 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
             begin_trace(L, sm, p, src, lc);
           }
         } else {
-        uint32_t tile = item >> 5, in_tile = item & 31u;
+        uint32_t grp, in_tile = item & 31u;
+        uint32_t tile = sched_tile(p.sched, item >> 5, f.total >> 5, grp);
         uint32_t band_local = tile / f.tiles_per_band, r = tile % f.tiles_per_band;
         uint32_t trow = r / f.tcols, tcol = r % f.tcols;
         uint32_t x = tcol * kTileW + (in_tile & (kTileW - 1));
@@ -520,6 +527,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
         if (x < f.W && y < f.H) {
           uint32_t pix = y * f.W + x;
           sm.u(C_PIX) = pix;
+          if (COST) sm.u(C_GRP) = (in_tile & 7u) ? 0xFFFFFFFFu : grp, sm.u(C_T0) = 0u;
           sm.put3(C_COLX, mk3(0, 0, 0));
           begin_sample<MODE>(L, sm, p, pix, 0, lc);
         }
@@ -536,7 +544,8 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
 
 template <uint32_t MODE, bool STRICT, bool STATS>
 int launch_m(const RenderA &p, int num_sms, cudaStream_t stream) {
-  auto kern = k_render_m<MODE, STRICT, STATS>;
+  // the cost-recording build runs only on the frames that re-measure the schedule (p.sched.cost set), and never for rays
+  auto kern = (MODE != kModeTrace && p.sched.cost) ? k_render_m<MODE, STRICT, STATS, MODE != kModeTrace> : k_render_m<MODE, STRICT, STATS, false>;
   int per_sm = 0;
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, 0);
   if (e != cudaSuccess) return -(int)e;

@@ -34,6 +34,19 @@ struct Partition {
   uint32_t rank = 0, world = 1, band_rows = 8;
 };
 
+// Frame-to-frame schedule feedback: the tiles of a frame are cut into groups of consecutive tiles; every group
+// records the longest time one of its pixels (layout A: a lane of the state machine) or tiles (layout B: a warp) was occupied,
+// and the next frame hands the groups out in descending order of that latency, so that the slowest rays of the image (rays
+// grazing the geometry near a horizon take 50-100x the median) start first instead of forming the tail of the launch.
+// order == nullptr: row-major order.
+struct TileSchedule {
+  const uint32_t *order;    // device: schedule position -> group
+  uint32_t *cost;           // device: per group, the largest per-pixel (A: traversal steps) / per-tile (B: SM clocks) cost seen by
+                            // this launch (zeroed by the host); nullptr on frames that only apply the order
+  uint32_t group_shift, n_groups;   // a group = 2^group_shift consecutive tiles
+  uint32_t lead;            // tiles beyond n_groups << group_shift (the last tiles of the image): handed out first, no cost kept
+};
+
 struct WorkCounters {       // device-resident, zeroed before each run
   unsigned long long rays, box_tests, tri_tests, blas_entered, shaded_hits;
   unsigned long long errors;   // bit 0: a traversal stack overflowed (the run is reported as failed)
@@ -53,6 +66,7 @@ struct RenderA {
   uint32_t quorum_refill;   // ray state machine: run GEN/POST when fewer lanes than this are traversing
   uint32_t chunk;           //                    pixels a warp reserves per atomicAdd on the work counter
   uint32_t blocks_per_sm_cap;   //                resident blocks per SM to launch (0 = as many as fit)
+  TileSchedule sched;       // frame modes
   uint32_t quorum_inner;    //                    leave the inner-node loop when fewer lanes than this hold an inner node
   // hit-record mode of the state machine (launch_trace_machine): closest-hit records instead of pixels
   const float *rays;        // 6 floats per ray, or nullptr => primary rays of `arg`

@@ -124,6 +124,13 @@ __device__ __forceinline__ NodeBoxes load_boxes(const GpuNodeB *n) {
 __device__ __forceinline__ uint4 load_info(const GpuNodeB *n) {
   return __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint8_t *>(n) + 96));
 }
+// header + boxes of one node issued back to back (one 128-byte line, one round trip), before anything looks at the header
+__device__ __forceinline__ void load_node(const GpuNodeB *n, uint4 &info, NodeBoxes &b) {
+  const uint8_t *p = reinterpret_cast<const uint8_t *>(n);
+  float4 h = ldg4_pinned(p + 96);
+  b = NodeBoxes{ldg4_pinned(p), ldg4_pinned(p + 16), ldg4_pinned(p + 32), ldg4_pinned(p + 48), ldg4_pinned(p + 64), ldg4_pinned(p + 80)};
+  info = make_uint4(__float_as_uint(h.x), __float_as_uint(h.y), __float_as_uint(h.z), __float_as_uint(h.w));
+}
 __device__ __forceinline__ float comp(const float4 &v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
 
 // ray_box_intersect (:318-339) of child k; returns the reference's value (tmin, or LARGE_FLOAT on a miss; NaN stays NaN)
@@ -191,10 +198,11 @@ __device__ __forceinline__ void trace_fast(const RtuScene &sc, const Ray &wray, 
     bool ok = top ? (idx < sc.n_tlas) : (idx < sc.n_bvh);
     if (ok) {
       const GpuNodeB *n = (top ? sc.gtlas : sc.gbvh) + idx;
-      uint4 info = load_info(n);
+      uint4 info;
+      NodeBoxes b;
+      load_node(n, info, b);
       if (STATS) lc.box++;
       if (!(info.z & kFlagLeaf)) {
-        NodeBoxes b = load_boxes(n);
         const ObjRay &r = top ? world : in.ray;
         const uint32_t child0 = (top ? 0u : in.base) + info.x;
         float d[4];
@@ -534,6 +542,9 @@ __global__ void __launch_bounds__(kBlockThreads, STRICT ? 2 : VXB_RTU_MIN_BLOCKS
     if (lane == 0) tile = atomicAdd(p.tile_counter, 1u);
     tile = __shfl_sync(0xffffffffu, tile, 0);
     if (tile >= ntiles) break;
+    uint32_t grp;
+    tile = sched_tile(p.sched, tile, ntiles, grp);
+    const uint32_t t0 = (uint32_t)clock();
     uint32_t band_local = tile / tiles_per_band, r = tile % tiles_per_band;
     uint32_t trow = r / tcols, tcol = r % tcols;
     uint32_t x = tcol * kTileW + (lane & (kTileW - 1));
@@ -544,6 +555,8 @@ __global__ void __launch_bounds__(kBlockThreads, STRICT ? 2 : VXB_RTU_MIN_BLOCKS
       f3 color = shade_b<STRICT, STATS>(p.scene, a, ray, lc, stk_e, stk_d);
       p.out[y * W + x] = rgb32f_to_rgb8(color);
     }
+    __syncwarp();
+    if (lane == 0 && grp != 0xFFFFFFFFu && p.sched.cost) atomicMax(p.sched.cost + grp, (uint32_t)clock() - t0);   // longest tile of the group
   }
   flush_counters(p.counters, lc, STATS);
 }

@@ -48,6 +48,7 @@ struct RtuRender {
   WorkCounters *counters;
   uint32_t *tile_counter;
   int stats;
+  TileSchedule sched;       // frame-to-frame schedule feedback (rt_raycast.h)
 };
 
 struct RtuTrace {

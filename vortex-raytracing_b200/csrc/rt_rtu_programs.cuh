@@ -122,6 +122,9 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_PROGRAM_MIN_BLOCKS) k_rtu_p
     if (lane == 0) tile = atomicAdd(p.tile_counter, 1u);
     tile = __shfl_sync(0xffffffffu, tile, 0);
     if (tile >= ntiles) break;
+    uint32_t grp;
+    tile = sched_tile(p.sched, tile, ntiles, grp);
+    const uint32_t t0 = (uint32_t)clock();
     uint32_t band_local = tile / tiles_per_band, r = tile % tiles_per_band;
     uint32_t trow = r / tcols, tcol = r % tcols;
     uint32_t x = tcol * kTileW + (lane & (kTileW - 1));
@@ -136,6 +139,8 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_PROGRAM_MIN_BLOCKS) k_rtu_p
       while (!payload.done && (work = rt.getWork()) != 0) sbt_call<P>(rt, work, a);
       p.out[y * W + x] = rgb32f_to_rgb8(payload.color);
     }
+    __syncwarp();
+    if (lane == 0 && grp != 0xFFFFFFFFu && p.sched.cost) atomicMax(p.sched.cost + grp, (uint32_t)clock() - t0);
   }
   flush_counters(p.counters, lc, STATS);
 }

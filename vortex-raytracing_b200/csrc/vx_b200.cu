@@ -114,6 +114,7 @@ public:
     pipe_free_locked();
     alt_free_locked();
     ray_order_free_locked();
+    sched_free_locked();
     if (counters_) cudaFree(counters_);
     if (tile_counter_) cudaFree(tile_counter_);
     if (h_counters_) cudaFreeHost(h_counters_);
@@ -534,6 +535,12 @@ private:
   }
   int end_run_locked() {
     CUDA_TRY(cudaEventRecord(ev_end_, stream_));
+    if (sched_active_ >= 0) {   // group costs of this frame, read by the next sched_prepare_locked
+      SchedState &st = sched_[sched_active_];
+      CUDA_TRY(cudaMemcpyAsync(st.h_cost, st.d_cost, st.n_groups * 4, cudaMemcpyDeviceToHost, stream_));
+      st.pending = true;
+      sched_active_ = -1;
+    }
     CUDA_TRY(cudaMemcpyAsync(h_counters_, counters_, sizeof(WorkCounters), cudaMemcpyDeviceToHost, stream_));
     run_pending_ = true;
     return 0;
@@ -558,6 +565,10 @@ private:
     stats_.prep_launches = prep_launches_;
     stats_.prep_ms = ms_prep;
     stats_.kernel_ms = ms_total - ms_prep;
+    if (sched_timed_ >= 0) {   // the two halves of the schedule trial
+      (sched_timed_phase_ == 1 ? sched_[sched_timed_].ms_identity : sched_[sched_timed_].ms_ordered) = stats_.kernel_ms;
+      sched_timed_ = -1;
+    }
     return 0;
   }
 
@@ -679,6 +690,8 @@ private:
       resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &dummy, &bvh_bytes);
       bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes ||
                     (dcr_get(VX_DCR_B200_RT_ORDER) == 0 && !sc.wide);
+      // the prep-time event is already recorded: the schedule's small copies count as kernel time
+      if (sched_prepare_locked(0, a.dst_width, a.dst_height, !simple && p.chunk == 32, &p.sched) != 0) return -1;
       rc = simple ? launch_render_a(p, prop_.multiProcessorCount, stream_) : launch_render_machine(p, prop_.multiProcessorCount, stream_);
     } else {
       uint64_t bvh_bytes = 0;
@@ -806,6 +819,7 @@ private:
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.part = part_, p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
     p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
+    if (sched_prepare_locked(1, a.dst_width, a.dst_height, true, &p.sched) != 0) return -1;
     // VX_DCR_B200_RT_KERNEL: 0 = the fused kernel; 2 + n = shader program n through the traceRay/getWork/getAttr/commit
     // shim (vx_raytrace_b200.cuh; program 0 = the three shipped shaders, rt_rtu_programs.cuh)
     uint32_t kernel = dcr_get(VX_DCR_B200_RT_KERNEL);
@@ -922,6 +936,112 @@ private:
       if (x.ev_end) cudaEventDestroy(x.ev_end);
       x = RunCtx{};
     }
+  }
+
+  // ---- frame-to-frame schedule feedback (TileSchedule, rt_raycast.h) ----
+  // A cycle of kSchedCycle frames of one (layout, image size, partition): frames 0 and 1 run in row-major order and record the
+  // groups' costs, frame 2 runs in descending-cost order, and the faster of frames 1 and 2 (kernel time, 2 % margin) is kept
+  // for the rest of the cycle.  While the order is in use layout B refreshes the costs every frame (a clock read per tile);
+  // layout A records them with a slower build of its kernel, on the trial frames and every 16th.
+  static constexpr uint32_t kSchedCycle = 64;
+  struct SchedState {
+    uint64_t key[5] = {0, 0, 0, 0, 0};
+    bool valid = false, pending = false, use_order = false, identity_loaded = true;
+    uint32_t group_shift = 0, n_groups = 0, lead = 0, frames = 0;
+    float ms_identity = 0, ms_ordered = 0;
+    uint32_t *d_order = nullptr, *d_cost = nullptr, *h_cost = nullptr;
+    std::vector<uint32_t> order;      // descending cost, from the last measured frame
+  } sched_[2];   // [0] layout A frames, [1] layout B frames
+  int sched_active_ = -1;   // which state the run in flight records costs for
+  int sched_timed_ = -1;    // which state wants this run's kernel time, and as what
+  uint32_t sched_timed_phase_ = 0;
+  void sched_free_locked() {
+    for (auto &st : sched_) {
+      if (st.d_order) cudaFree(st.d_order);
+      if (st.d_cost) cudaFree(st.d_cost);
+      if (st.h_cost) cudaFreeHost(st.h_cost);
+      st = SchedState{};
+    }
+  }
+  // Tiles of this rank exactly as the kernels enumerate them (8x4 tiles inside this rank's bands).
+  uint32_t rank_tiles(uint32_t W, uint32_t H) const {
+    const uint32_t tcols = (W + 7) / 8, bands_total = (H + part_.band_rows - 1) / part_.band_rows;
+    const uint32_t bands = bands_total > part_.rank ? (bands_total - part_.rank + part_.world - 1) / part_.world : 0;
+    return bands * (part_.band_rows / 4) * tcols;
+  }
+  int sched_upload_locked(SchedState &st, bool identity) {
+    if (identity) {
+      std::vector<uint32_t> id(st.n_groups);
+      for (uint32_t i = 0; i < st.n_groups; i++) id[i] = i;
+      CUDA_TRY(cudaMemcpyAsync(st.d_order, id.data(), st.n_groups * 4, cudaMemcpyHostToDevice, stream_));   // pageable: staged before return
+    } else {
+      CUDA_TRY(cudaMemcpyAsync(st.d_order, st.order.data(), st.n_groups * 4, cudaMemcpyHostToDevice, stream_));
+    }
+    st.identity_loaded = identity;
+    return 0;
+  }
+  int sched_prepare_locked(int which, uint32_t W, uint32_t H, bool eligible, TileSchedule *out) {
+    *out = TileSchedule{};
+    sched_active_ = -1, sched_timed_ = -1;
+    const uint32_t ntiles = rank_tiles(W, H);
+    if (!eligible || ntiles < 2048 || env_u64("VORTEX_B200_SCHEDULE", 1) == 0) return 0;
+    SchedState &st = sched_[which];
+    const uint64_t key[5] = {W, H, part_.rank, part_.world, part_.band_rows};
+    if (!st.valid || memcmp(key, st.key, sizeof(key)) != 0) {
+      st.group_shift = 4;   // about 256 groups of 2^k tiles
+      while ((ntiles >> st.group_shift) > 256) st.group_shift++;
+      st.n_groups = ntiles >> st.group_shift;
+      st.lead = ntiles - (st.n_groups << st.group_shift);
+      if (st.d_order) cudaFree(st.d_order);
+      if (st.d_cost) cudaFree(st.d_cost);
+      if (st.h_cost) cudaFreeHost(st.h_cost);
+      st.d_order = st.d_cost = st.h_cost = nullptr;
+      CUDA_TRY(cudaMalloc(&st.d_order, st.n_groups * 4));
+      CUDA_TRY(cudaMalloc(&st.d_cost, st.n_groups * 4));
+      CUDA_TRY(cudaMallocHost(&st.h_cost, st.n_groups * 4));
+      st.order.assign(st.n_groups, 0);
+      memcpy(st.key, key, sizeof(key));
+      st.valid = true, st.pending = false, st.use_order = false, st.frames = 0;
+    }
+    const uint32_t phase = st.frames % kSchedCycle;
+    st.frames++;
+    if (st.pending) {   // costs of the last measured frame (complete: every run is finished before the next begins)
+      uint64_t sum = 0;
+      for (uint32_t i = 0; i < st.n_groups; i++) sum += st.h_cost[i];
+      if (getenv("VORTEX_B200_SCHED_DEBUG")) {
+        fprintf(stderr, "[sched %d] phase=%u groups=%u shift=%u lead=%u use=%d ms identity %.4f ordered %.4f cost:", which, phase, st.n_groups,
+                st.group_shift, st.lead, (int)st.use_order, st.ms_identity, st.ms_ordered);
+        for (uint32_t i = 0; i < st.n_groups; i += 8) fprintf(stderr, " %u", st.h_cost[i]);
+        fprintf(stderr, "\n");
+      }
+      if (sum) {
+        for (uint32_t i = 0; i < st.n_groups; i++) st.order[i] = i;
+        const uint32_t *c = st.h_cost;
+        std::stable_sort(st.order.begin(), st.order.end(), [c](uint32_t a, uint32_t b) { return c[a] > c[b]; });
+      }
+      st.pending = false;
+    }
+    bool identity;
+    if (phase <= 1) identity = true;                       // frame 0 warms up and records the costs, frame 1 is the timed row-major half
+    else if (phase == 2) identity = false;                 // the timed descending-cost half
+    else {
+      if (phase == 3) st.use_order = st.ms_ordered > 0 && st.ms_ordered < 0.98f * st.ms_identity;
+      identity = !st.use_order;
+    }
+    if (st.frames == 1 || identity != st.identity_loaded || !identity) {   // (the descending order may have been refreshed)
+      if (sched_upload_locked(st, identity) != 0) return -1;
+    }
+    const bool measure = phase < 3 || (st.use_order && (which == 1 || (phase & 15u) == 0));
+    if (identity && !measure) return 0;                    // row-major order, nothing recorded: the kernels' plain path
+    out->order = st.d_order, out->cost = nullptr;
+    out->group_shift = st.group_shift, out->n_groups = st.n_groups, out->lead = st.lead;
+    if (measure) {
+      CUDA_TRY(cudaMemsetAsync(st.d_cost, 0, st.n_groups * 4, stream_));
+      out->cost = st.d_cost;
+      sched_active_ = which;
+    }
+    if (phase == 1 || phase == 2) sched_timed_ = which, sched_timed_phase_ = phase;
+    return 0;
   }
 
   // coherence ordering scratch (grow-only)

@@ -81,10 +81,11 @@ __device__ bool fast_advance(const RtuScene &sc, const Ray &wray, FastWalk &w, c
     const uint32_t idx = cur & ~kTlasBit;
     if (!(top ? (idx < sc.n_tlas) : (idx < sc.n_bvh))) continue;
     const GpuNodeB *n = (top ? sc.gtlas : sc.gbvh) + idx;
-    uint4 info = load_info(n);
+    uint4 info;
+    NodeBoxes b;
+    load_node(n, info, b);
     if (STATS) lc.box++;
     if (!(info.z & kFlagLeaf)) {
-      NodeBoxes b = load_boxes(n);
       const ObjRay &r = top ? w.world : w.in.ray;
       const uint32_t child0 = (top ? 0u : w.in.base) + info.x;
       const float inf = __int_as_float(0x7F800000);
