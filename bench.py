@@ -385,6 +385,8 @@ def run_b200(args, wl, name):
                 "config": {"workload": name, "baseline_config_index": wl["config_index"], "width": W, "height": H,
                            "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32, "mode": wl["mode"], "max_depth": wl["depth"],
                            "rays_per_step": rays_step, "partition": f"{BAND_ROWS}-row bands round-robin over {world} GPU(s), scene replicated",
+                           "schedule_feedback": "on: tile groups handed out in descending order of the cost recorded on earlier frames when "
+                                                "a timed trial during warm-up found that faster (DESIGN 5; VORTEX_B200_SCHEDULE=0 disables)",
                            "framebuffer_transport": ("none (single GPU)" if world == 1 else
                                                      "kernels store into rank 0's framebuffer over NVLink peer memory (CUDA IPC)" if p2p else
                                                      "NCCL gather inside the timed region"), **check,

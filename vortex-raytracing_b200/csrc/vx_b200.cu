@@ -949,7 +949,8 @@ private:
     bool valid = false, pending = false, use_order = false, identity_loaded = true;
     uint32_t group_shift = 0, n_groups = 0, lead = 0, frames = 0;
     float ms_identity = 0, ms_ordered = 0;
-    uint32_t *d_order = nullptr, *d_cost = nullptr, *h_cost = nullptr;
+    uint32_t *d_order = nullptr, *d_cost = nullptr, *h_cost = nullptr, *h_order = nullptr;
+    bool order_dirty = false;
     std::vector<uint32_t> order;      // descending cost, from the last measured frame
   } sched_[2];   // [0] layout A frames, [1] layout B frames
   int sched_active_ = -1;   // which state the run in flight records costs for
@@ -960,6 +961,7 @@ private:
       if (st.d_order) cudaFree(st.d_order);
       if (st.d_cost) cudaFree(st.d_cost);
       if (st.h_cost) cudaFreeHost(st.h_cost);
+      if (st.h_order) cudaFreeHost(st.h_order);
       st = SchedState{};
     }
   }
@@ -969,15 +971,12 @@ private:
     const uint32_t bands = bands_total > part_.rank ? (bands_total - part_.rank + part_.world - 1) / part_.world : 0;
     return bands * (part_.band_rows / 4) * tcols;
   }
+  // h_order is page-locked (a pageable source would make the copy wait for the stream's earlier work) and is rewritten only
+  // here, after the previous run has been finished, so the asynchronous copy never races a modification
   int sched_upload_locked(SchedState &st, bool identity) {
-    if (identity) {
-      std::vector<uint32_t> id(st.n_groups);
-      for (uint32_t i = 0; i < st.n_groups; i++) id[i] = i;
-      CUDA_TRY(cudaMemcpyAsync(st.d_order, id.data(), st.n_groups * 4, cudaMemcpyHostToDevice, stream_));   // pageable: staged before return
-    } else {
-      CUDA_TRY(cudaMemcpyAsync(st.d_order, st.order.data(), st.n_groups * 4, cudaMemcpyHostToDevice, stream_));
-    }
-    st.identity_loaded = identity;
+    for (uint32_t i = 0; i < st.n_groups; i++) st.h_order[i] = identity ? i : st.order[i];
+    CUDA_TRY(cudaMemcpyAsync(st.d_order, st.h_order, st.n_groups * 4, cudaMemcpyHostToDevice, stream_));
+    st.identity_loaded = identity, st.order_dirty = false;
     return 0;
   }
   int sched_prepare_locked(int which, uint32_t W, uint32_t H, bool eligible, TileSchedule *out) {
@@ -995,10 +994,12 @@ private:
       if (st.d_order) cudaFree(st.d_order);
       if (st.d_cost) cudaFree(st.d_cost);
       if (st.h_cost) cudaFreeHost(st.h_cost);
-      st.d_order = st.d_cost = st.h_cost = nullptr;
+      if (st.h_order) cudaFreeHost(st.h_order);
+      st.d_order = st.d_cost = st.h_cost = st.h_order = nullptr;
       CUDA_TRY(cudaMalloc(&st.d_order, st.n_groups * 4));
       CUDA_TRY(cudaMalloc(&st.d_cost, st.n_groups * 4));
       CUDA_TRY(cudaMallocHost(&st.h_cost, st.n_groups * 4));
+      CUDA_TRY(cudaMallocHost(&st.h_order, st.n_groups * 4));
       st.order.assign(st.n_groups, 0);
       memcpy(st.key, key, sizeof(key));
       st.valid = true, st.pending = false, st.use_order = false, st.frames = 0;
@@ -1018,6 +1019,7 @@ private:
         for (uint32_t i = 0; i < st.n_groups; i++) st.order[i] = i;
         const uint32_t *c = st.h_cost;
         std::stable_sort(st.order.begin(), st.order.end(), [c](uint32_t a, uint32_t b) { return c[a] > c[b]; });
+        st.order_dirty = true;
       }
       st.pending = false;
     }
@@ -1028,7 +1030,7 @@ private:
       if (phase == 3) st.use_order = st.ms_ordered > 0 && st.ms_ordered < 0.98f * st.ms_identity;
       identity = !st.use_order;
     }
-    if (st.frames == 1 || identity != st.identity_loaded || !identity) {   // (the descending order may have been refreshed)
+    if (st.frames == 1 || identity != st.identity_loaded || (!identity && st.order_dirty)) {
       if (sched_upload_locked(st, identity) != 0) return -1;
     }
     const bool measure = phase < 3 || (st.use_order && (which == 1 || (phase & 15u) == 0));
