@@ -35,7 +35,7 @@ namespace {
 using namespace dev;
 
 #ifndef VXB_RTU_MIN_BLOCKS
-#define VXB_RTU_MIN_BLOCKS 3
+#define VXB_RTU_MIN_BLOCKS 4   // 64 registers: +3-6 % once the schedule feedback removed the tail (no gain before it)
 #endif
 constexpr uint32_t kFlagTlas = 1u, kFlagLeaf = 2u;
 constexpr uint32_t kStackB = 96;          // fast-order stack entries (3 pushes per level at most)
