@@ -108,7 +108,8 @@ public:
     if (gtri_) cudaFree(gtri_);
     if (wide_) cudaFree(wide_);
     if (wide_bases_) cudaFree(wide_bases_);
-    wide_ = nullptr, wide_bases_ = nullptr, wide_valid_ = false;
+    if (wide_bases_host_) cudaFreeHost(wide_bases_host_);
+    wide_ = nullptr, wide_bases_ = nullptr, wide_bases_host_ = nullptr, wide_valid_ = false;
     if (rtu_nodes_) cudaFree(rtu_nodes_);
     if (rtu_tri_) cudaFree(rtu_tri_);
     pipe_free_locked();
@@ -639,8 +640,15 @@ private:
         if (!wide_valid_ || memcmp(key, wide_key_, sizeof(key)) != 0) {
           // instance bases: the bvh_offset field of every blas_node_t (child indices are instance-local)
           std::vector<uint8_t> hb(n_blas * sizeof(BlasNodeA));
-          CUDA_TRY(cudaMemcpyAsync(hb.data(), blas_raw, hb.size(), cudaMemcpyDeviceToHost, stream_));
-          CUDA_TRY(cudaStreamSynchronize(stream_));
+          uint64_t bstart = 0;
+          space_.find(a.blas_addr, 1, &bstart);
+          auto sh = small_shadow_.find(bstart);
+          if (sh != small_shadow_.end() && sh->second.size() >= (a.blas_addr - bstart) + hb.size()) {
+            memcpy(hb.data(), sh->second.data() + (a.blas_addr - bstart), hb.size());   // host copy kept at upload time (<= 4 KB uploads)
+          } else {
+            CUDA_TRY(cudaMemcpyAsync(hb.data(), blas_raw, hb.size(), cudaMemcpyDeviceToHost, stream_));
+            CUDA_TRY(cudaStreamSynchronize(stream_));
+          }
           std::vector<uint32_t> bases;
           for (uint64_t i = 0; i < n_blas; ++i) {
             uint32_t off;
@@ -658,12 +666,15 @@ private:
           }
           if (wide_bases_cap_ < bases.size()) {
             if (wide_bases_) cudaFree(wide_bases_);
-            wide_bases_ = nullptr, wide_bases_cap_ = 0;
+            if (wide_bases_host_) cudaFreeHost(wide_bases_host_);
+            wide_bases_ = nullptr, wide_bases_host_ = nullptr, wide_bases_cap_ = 0;
             CUDA_TRY(cudaMalloc(&wide_bases_, bases.size() * 4));
+            CUDA_TRY(cudaMallocHost(&wide_bases_host_, bases.size() * 4));
             wide_bases_cap_ = bases.size();
           }
-          CUDA_TRY(cudaMemcpyAsync(wide_bases_, bases.data(), bases.size() * 4, cudaMemcpyHostToDevice, stream_));
-          CUDA_TRY(cudaStreamSynchronize(stream_));   // `bases` is a local
+          // page-locked staging, rewritten only after the previous run was finished: the copy needs no host wait
+          memcpy(wide_bases_host_, bases.data(), bases.size() * 4);
+          CUDA_TRY(cudaMemcpyAsync(wide_bases_, wide_bases_host_, bases.size() * 4, cudaMemcpyHostToDevice, stream_));
           CUDA_TRY(launch_build_wide(nodes, n_nodes, wide_bases_, (uint32_t)bases.size(), wide_, stream_));
           memcpy(wide_key_, key, sizeof(key));
           wide_valid_ = true;
@@ -1093,7 +1104,7 @@ private:
   uint64_t gtri_key_[4] = {0, 0, 0, 0};
   // layout-A 4-wide records (fast order of the state machine)
   GpuNode4 *wide_ = nullptr;
-  uint32_t *wide_bases_ = nullptr;
+  uint32_t *wide_bases_ = nullptr, *wide_bases_host_ = nullptr;
   uint64_t wide_cap_ = 0, wide_bases_cap_ = 0, wide_key_[5] = {0};
   bool wide_valid_ = false;
   // layout-B decoded nodes (TLAS then BLAS) and edge-form triangles
