@@ -284,3 +284,43 @@ def test_unmodified_reference_app_runs_on_b200(tmp_path, flags, md5, order):
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     assert r.returncode == 0, r.stdout
     assert hashlib.md5(out.read_bytes()).hexdigest() == md5, r.stdout[-400:]
+
+
+def test_schedule_feedback_keeps_the_frame():
+    """frame-to-frame schedule feedback: frames 0-1 run row-major, frame 2 in descending-cost order, later frames in
+    whichever order won the trial — the picture must be the same in every phase, for the whole image and for a band partition,
+    and equal to a run with the feedback disabled"""
+    port = po.PortRaycast() if po.have_port() else best_oracle()
+    sc = port.scene_create([scenes.heightfield(96), scenes.icosphere((0, 0.4, 0), 0.3, 2, reflectivity=0.5)])
+    karg = sc.setup(960, 540, max_depth=2)
+    os.environ["VORTEX_B200_SCHEDULE"] = "0"
+    try:
+        tr = tracer_for(sc, karg)
+        try:
+            tr.set_mode(1, 0)
+            want = tr.run().copy()
+        finally:
+            tr.close()
+    finally:
+        os.environ.pop("VORTEX_B200_SCHEDULE", None)
+    tr = tracer_for(sc, karg)
+    try:
+        for mode in (1, 0):
+            tr.set_mode(mode, 0)
+            ref = want if mode == 1 else None
+            for frame in range(6):
+                got = tr.run()
+                if ref is None:
+                    ref = got.copy()
+                assert np.array_equal(got, ref), (mode, frame)
+        tr.set_mode(1, 0)
+        parts = np.zeros_like(want)
+        for rank in range(2):
+            tr.dev.set_partition(rank, 2, 8)
+            for frame in range(5):
+                got = tr.run()
+            rows = np.concatenate([np.arange(b * 8, min(b * 8 + 8, 540)) for b in range(rank, (540 + 7) // 8, 2)])
+            parts[rows] = got[rows]
+        assert np.array_equal(parts, want)
+    finally:
+        tr.close()

@@ -267,3 +267,33 @@ def test_unmodified_reference_raytracing_app_runs_on_b200(tmp_path, order):
     assert (want != background).mean() > 0.1                                   # the teapot is in the picture
     assert channel_diff(got, want) <= 1
     assert (got == want).mean() > 0.999
+
+
+def test_rtu_schedule_feedback_keeps_the_frame():
+    """layout B: the frame is the same in every phase of the schedule feedback (row-major trial frames, descending-cost order,
+    the kept order), for the fused kernel and for the shader-program kernel, and equals a run with the feedback disabled"""
+    import importlib
+    from rt_common import scenes
+    from rtu_common import b_mesh
+    host = importlib.import_module("vortex-raytracing_b200.host")
+    hs = host.RtxHostScene([b_mesh(scenes.heightfield(96), two_materials=True),
+                            b_mesh(scenes.icosphere((0, 0.5, 0), 0.4, 2), diffuse=(0.2, 0.6, 0.9), reflectivity=0.5)])
+    karg = hs.setup(960, 540, max_depth=2)
+    bufs = hs.buffers()
+    os.environ["VORTEX_B200_SCHEDULE"] = "0"
+    try:
+        tr = tracer_b(bufs, karg, 1)
+        try:
+            want = tr.run().copy()
+        finally:
+            tr.close()
+    finally:
+        os.environ.pop("VORTEX_B200_SCHEDULE", None)
+    tr = tracer_b(bufs, karg, 1)
+    try:
+        for program in (None, 0):
+            tr.set_program(program)
+            for frame in range(6):
+                assert np.array_equal(tr.run(), want), (program, frame)
+    finally:
+        tr.close()
