@@ -401,7 +401,11 @@ def run_b200(args, wl, name):
                              "algorithmic_bytes_per_launch": abytes, "algorithmic_bytes_per_ray": abytes / max(1, work["rays"]),
                              "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
                                       "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},
-                             "work_per_ray": {k: work[k] / max(1, work["rays"]) for k in ("box_tests", "tri_tests", "blas_entered", "shaded_hits")}},
+                             "work_per_ray": {k: work[k] / max(1, work["rays"]) for k in ("box_tests", "tri_tests", "blas_entered", "shaded_hits")},
+                             "note": "achieved = the REFERENCE algorithm's bytes for the counted work (strict-order counters) / kernel time, as "
+                                     "the contract defines it; those bytes are served from L1/L2 (`traffic` is what reached DRAM) and the "
+                                     "4-wide records read fewer of them, so frac can exceed 1 — the binding resource is instruction issue "
+                                     "(ncu: 80 % issue-active, profiles/r01_ncu_machine_cfg1_sched.txt)"},
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if tr is not None:
