@@ -156,6 +156,10 @@ int vx_b200_set_remote_framebuffer(vx_device_h hdevice, const void *ipc_handle_6
 /* Raw CUDA device pointer behind a Vortex buffer (for NCCL / torch interop on the same process). */
 int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr);
 
+/* Tell the runtime that a buffer's device memory was written without vx_copy_to_dev (an NCCL receive into
+ * vx_b200_device_ptr, a peer's store): the GPU-side records derived from it are rebuilt at the next vx_start. */
+int vx_b200_mark_written(vx_buffer_h hbuffer);
+
 /* The CUDA stream (cudaStream_t as integer) all of this device's kernels and copies are issued on. */
 int vx_b200_stream(vx_device_h hdevice, uint64_t *cuda_stream);
 

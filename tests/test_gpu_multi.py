@@ -26,3 +26,6 @@ def test_p2p_framebuffer_equals_nccl_gather():
     assert line["n_gpus"] == 2
     assert line["config"]["p2p_frame_equals_nccl_gather_frame"] is True
     assert "peer memory" in line["config"]["framebuffer_transport"]
+    # the end-to-end leg replicates the scene by NCCL broadcast from rank 0 (+ vx_b200_mark_written): same frame
+    assert line["config"]["e2e_frame_equals_checked_frame"] is True
+    assert "broadcast" in line["config"]["scene_replication"]

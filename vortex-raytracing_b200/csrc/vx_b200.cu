@@ -455,6 +455,17 @@ public:
     if (nodes_used) *nodes_used = used;
     return 0;
   }
+  // the buffer's device memory was written behind the runtime's back (NCCL receive, a peer's store): bump its upload
+  // generation so the caches keyed on it rebuild, and drop the host shadow of small uploads
+  int mark_written(uint64_t addr) {
+    std::lock_guard<std::mutex> g(mu_);
+    uint64_t start = 0;
+    auto *b = space_.find(addr, 1, &start);
+    if (!b) return fail("vx_b200_mark_written: not a live buffer");
+    b->write_gen = ++generation_;
+    small_shadow_.erase(start);
+    return 0;
+  }
   int set_remote_framebuffer(const void *handle, uint64_t offset, uint64_t bytes) {
     std::lock_guard<std::mutex> g(mu_);
     CUDA_TRY(cudaSetDevice(cuda_dev_));
@@ -1411,6 +1422,11 @@ VXB_EXPORT int vx_b200_export_buffer(vx_buffer_h hbuffer, void *ipc_handle_64, u
 VXB_EXPORT int vx_b200_set_remote_framebuffer(vx_device_h h, const void *ipc_handle_64, uint64_t offset, uint64_t bytes) {
   if (!h) return -1;
   return ((Device *)h)->set_remote_framebuffer(ipc_handle_64, offset, bytes);
+}
+VXB_EXPORT int vx_b200_mark_written(vx_buffer_h hbuffer) {
+  if (!hbuffer) return -1;
+  auto b = (Buffer *)hbuffer;
+  return b->device->mark_written(b->addr);
 }
 VXB_EXPORT int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr) {
   if (!hbuffer || !cuda_ptr) return -1;

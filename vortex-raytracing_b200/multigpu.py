@@ -92,6 +92,28 @@ def unshare_framebuffer(tracer, rank, world, owner=0):
         tracer.dev.set_remote_framebuffer(None)
 
 
+def scene_tensors(tracer, cuda_device):
+    """the tracer's device scene buffers as flat uint8 torch tensors (aliases, no copy), in upload order"""
+    out = {}
+    for name, b in tracer.bufs.items():
+        if b.size:
+            out[name] = torch.as_tensor(DeviceArray(b.device_ptr, (b.size,), "|u1"), device=torch.device("cuda", cuda_device))
+    return out
+
+
+def broadcast_scene(tracer, tensors, rank, world, src=0, group=None):
+    """Scene replication without N host uploads: rank `src` has uploaded the scene through vx_copy_to_dev; every other rank
+    receives the same bytes into its own vx buffers over NVLink (one NCCL broadcast per buffer) and tells its runtime that the
+    buffers changed (vx_b200_mark_written), so that its GPU-side records are rebuilt exactly as after an upload."""
+    if world == 1:
+        return
+    for name, t in tensors.items():
+        dist.broadcast(t, src=src, group=group)
+    if rank != src:
+        for name in tensors:
+            tracer.bufs[name].mark_written()
+
+
 class DeviceArray:
     """Wraps a raw device pointer of the vx arena (vx_b200_device_ptr) as a __cuda_array_interface__ provider so that
     torch.as_tensor can alias it without a copy (plumbing for NCCL; torch never computes on it)."""
