@@ -329,9 +329,22 @@ def run_b200(args, wl, name):
         if rank == 0:
             tr.out.copy_from_dev((out_pinned.data_ptr(), W * H * 4))
 
-    e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(2):
+    # warm-up of the end-to-end sequence: the first host->device copies of a process run at ~14 GB/s and reach the link rate
+    # (~50 GB/s) only after the GPU has seen some tens of ms of work (tools/quick_upload_probe2.py, profiles/r01_upload_ramp.txt),
+    # so the untimed steps cover that ramp: at least W steps and at least 0.15 s, the same count on every rank
+    e2e_steps = max(3, min(args.steps, 20))
+    e2e_warm = max(3, args.warmup)
+    t_w = time.perf_counter()
+    for _ in range(e2e_warm):
         e2e_step()
+    sync_all()
+    per_step = max((time.perf_counter() - t_w) / e2e_warm, 1e-4)
+    more = torch.tensor([min(200, max(0, int(0.15 / per_step) - e2e_warm))], dtype=torch.int64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(more, op=dist.ReduceOp.MAX)
+    for _ in range(int(more.item())):
+        e2e_step()
+    e2e_warm += int(more.item())
     sync_all()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -407,7 +420,7 @@ def run_b200(args, wl, name):
                            "l2": "512 MB memset between timed iterations (L2 flush); timed per step with CUDA events on the launch stream",
                            "host_bvh_build_s": round(build_s, 3), "extra_workloads": extra},
                 "clocks": clocks,
-                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "warmup": e2e_warm,
                         "timer": "host wall clock around the synchronous vx_* calls, max over ranks", "launches_per_step": e2e_launches},
                 "gpu_launches": int(launches_per_step) * args.steps, "rt_unit_perf": unit_perf,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
