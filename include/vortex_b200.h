@@ -160,6 +160,11 @@ int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr);
  * vx_b200_device_ptr, a peer's store): the GPU-side records derived from it are rebuilt at the next vx_start. */
 int vx_b200_mark_written(vx_buffer_h hbuffer);
 
+/* Measurement aid (no reference counterpart): bandwidth of random gathers of `record_bytes` (32 or 128) over a scratch buffer
+ * of `buffer_bytes` — L2-resident when it is well under the 126 MB L2, HBM-bound beyond.  This is the "L2 -> SM gather" roofline
+ * denominator of the traversal kernels; bench.py reports it next to the HBM and FP32 ones. */
+int vx_b200_probe_gather(vx_device_h hdevice, uint64_t buffer_bytes, uint32_t record_bytes, double *gbs);
+
 /* The CUDA stream (cudaStream_t as integer) all of this device's kernels and copies are issued on. */
 int vx_b200_stream(vx_device_h hdevice, uint64_t *cuda_stream);
 

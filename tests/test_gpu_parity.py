@@ -324,3 +324,18 @@ def test_schedule_feedback_keeps_the_frame():
         assert np.array_equal(parts, want)
     finally:
         tr.close()
+
+
+@pytest.mark.gpu
+def test_gpu_gather_probe_reports_a_bandwidth():
+    """vx_b200_probe_gather (roofline denominator): positive, 128-byte records move at least as many bytes as 32-byte ones, bad
+    record sizes are refused"""
+    dev = vx.Device()
+    try:
+        g32 = dev.probe_gather(32 << 20, 32)
+        g128 = dev.probe_gather(32 << 20, 128)
+        assert g32 > 100.0 and g128 >= g32 * 0.9, (g32, g128)
+        with pytest.raises(vx.VxError):
+            dev.probe_gather(32 << 20, 48)
+    finally:
+        dev.close()

@@ -24,6 +24,7 @@
 #include "rt_raycast.h"
 #include "rt_rtu.h"
 #include "rt_build.h"
+#include "rt_probe.h"
 #include <algorithm>
 
 #define VXB_EXPORT extern "C" __attribute__((visibility("default")))
@@ -457,6 +458,15 @@ public:
   }
   // the buffer's device memory was written behind the runtime's back (NCCL receive, a peer's store): bump its upload
   // generation so the caches keyed on it rebuild, and drop the host shadow of small uploads
+  // roofline denominator: random-record gather bandwidth out of L2 (or HBM, for a buffer beyond L2); diagnostics only
+  int probe_gather(uint64_t buffer_bytes, uint32_t record_bytes, double *gbs) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    if (finish_run_locked() != 0) return -1;
+    cudaError_t e = vxb::probe_gather(buffer_bytes, record_bytes, prop_.multiProcessorCount, stream_, gbs);
+    if (e != cudaSuccess) return fail("vx_b200_probe_gather: %s", cudaGetErrorString(e));
+    return 0;
+  }
   int mark_written(uint64_t addr) {
     std::lock_guard<std::mutex> g(mu_);
     uint64_t start = 0;
@@ -1427,6 +1437,10 @@ VXB_EXPORT int vx_b200_mark_written(vx_buffer_h hbuffer) {
   if (!hbuffer) return -1;
   auto b = (Buffer *)hbuffer;
   return b->device->mark_written(b->addr);
+}
+VXB_EXPORT int vx_b200_probe_gather(vx_device_h h, uint64_t buffer_bytes, uint32_t record_bytes, double *gbs) {
+  if (!h || !gbs) return -1;
+  return ((Device *)h)->probe_gather(buffer_bytes, record_bytes, gbs);
 }
 VXB_EXPORT int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr) {
   if (!hbuffer || !cuda_ptr) return -1;

@@ -24,7 +24,7 @@ EXPORTS = (
     "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
-    "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_mark_written vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_mark_written vx_b200_probe_gather vx_b200_stream vx_b200_last_kernel_ms "
     "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_trace_rays_host vx_b200_last_error"
 ).split()
 
@@ -61,7 +61,7 @@ def lib():
             "vx_dcr_read": [H, u32, C.POINTER(u32)], "vx_dcr_write": [H, u32, u32], "vx_mpm_query": [H, u32, u32, C.POINTER(u64)],
             "vx_upload_kernel_bytes": [H, vp, u64, C.POINTER(B)], "vx_upload_kernel_file": [H, C.c_char_p, C.POINTER(B)],
             "vx_upload_bytes": [H, vp, u64, C.POINTER(B)], "vx_upload_file": [H, C.c_char_p, C.POINTER(B)],
-            "vx_b200_select_device": [i32], "vx_b200_set_partition": [H, u32, u32, u32], "vx_b200_device_ptr": [B, C.POINTER(u64)], "vx_b200_mark_written": [B],
+            "vx_b200_select_device": [i32], "vx_b200_set_partition": [H, u32, u32, u32], "vx_b200_device_ptr": [B, C.POINTER(u64)], "vx_b200_mark_written": [B], "vx_b200_probe_gather": [H, u64, u32, C.POINTER(C.c_double)],
             "vx_b200_stream": [H, C.POINTER(u64)], "vx_b200_last_kernel_ms": [H, C.POINTER(C.c_float)],
             "vx_b200_enable_stats": [H, i32], "vx_b200_get_stats": [H, C.POINTER(Stats)],
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
@@ -246,6 +246,12 @@ class Device:
     def last_kernel_ms(self):
         v = C.c_float()
         _check(lib().vx_b200_last_kernel_ms(self.h, C.byref(v)), "vx_b200_last_kernel_ms")
+        return v.value
+
+    def probe_gather(self, buffer_bytes=32 << 20, record_bytes=32):
+        """random-record gather bandwidth (GB/s) over a scratch buffer: the L2 -> SM roofline denominator (vx_b200_probe_gather)"""
+        v = C.c_double()
+        _check(lib().vx_b200_probe_gather(self.h, int(buffer_bytes), int(record_bytes), C.byref(v)), "vx_b200_probe_gather")
         return v.value
 
     def enable_stats(self, on=True):
