@@ -167,6 +167,21 @@ def cpu_frame_timer(wl, budget_s):
             n = (rows[1] - rows[0]) * wl["w"]      # reflectivity 0 in every benchmark scene: one ray per pixel
         return dt, n
 
+    # the reference as written is single-threaded (SURVEY.md 8d "CPU-1"): the same loop on one thread, over <= ~5 s of rows
+    n1 = min(nrows, max(8, int(5.0 / (per_row * threads)) // 8 * 8))
+    bands = [rows[0] + (i * (nrows // 8) // (n1 // 8)) * 8 for i in range(n1 // 8)]   # 8-row bands spread evenly over the sample's rows
+
+    def single():
+        dt, n = 0.0, 0
+        for y in bands:
+            t = time.perf_counter()
+            _, k = sc.render(mode=wl["mode"], rows=(y, y + 8), threads=1)
+            dt += time.perf_counter() - t
+            n += 8 * wl["w"] if wl["mode"] == 0 else k
+        return {"value": n / dt / 1e6, "unit": "Mrays/s", "cores": 1,
+                "sample": f"{len(bands)} bands of 8 rows spread evenly over rows {rows[0]}..{rows[1]}, one thread (the reference as written)"}
+
+    frame.single = single
     what = "whole frame" if nrows == H else f"rows {rows[0]}..{rows[1]} of {H}"
     return frame, kind, threads, f"{what} of {wl['w']}x{wl['h']}, all host threads"
 
@@ -419,6 +434,7 @@ def run_b200(args, wl, name):
             dt, n = frame()
             best = (dt, n) if best is None or dt < best[0] else best
         cpu = {"value": best[1] / best[0] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample + ", best of 2"}
+        cpu["single_thread"] = frame.single()
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),

@@ -45,4 +45,6 @@ total = time.perf_counter() - t_all
 for k, v in acc.items():
     print(f"{k:34s} {v / N * 1e6:9.1f} us")
 print(f"{'sum of calls':34s} {sum(acc.values()) / N * 1e6:9.1f} us   wall per frame {total / N * 1e6:.1f} us   kernel {tr.dev.last_kernel_ms() * 1e3:.1f} us")
+st = tr.dev.stats()
+print(f"last run: prep_ms {st['prep_ms']*1e3:.1f} us ({st['prep_launches']} launches), kernel_ms {st['kernel_ms']*1e3:.1f} us")
 tr.close()
