@@ -33,6 +33,9 @@ constexpr uint32_t F_ANY = 4, F_NAN = 8, F_INBLAS = 16, F_OCCL = 32;
 // the sweep in profiles/r01_sweep_quorum_chunk.txt): GEN/POST run when fewer than quorum_refill lanes are traversing, the
 // inner-node loop is left when fewer than quorum_inner lanes hold an inner node, a warp reserves `chunk` pixels (one 8x4
 // tile) per atomicAdd — 256-pixel chunks left SMs idle 32-39 % of the kernel (ncu sm__cycles_active avg vs elapsed).
+#ifndef VXB_SORT_MINMAX
+#define VXB_SORT_MINMAX 0
+#endif
 #ifndef VXB_MIN_BLOCKS
 #define VXB_MIN_BLOCKS 4
 #endif
@@ -156,11 +159,21 @@ __device__ __forceinline__ void step_wide(Lane &L, bool careful, uint32_t *stk_e
     d[3] = h ? t : kInf;   // unused slots hold NaN boxes: every comparison of the slab test fails
   }
   if (STATS) lc.box += 4;
+#if VXB_SORT_MINMAX   // compare-exchange without moves: distances through min/max (never NaN here), cursors through two selects
+#define VXB_CSWAP(i, j)                                     \
+  {                                                         \
+    const bool sw = d[j] < d[i];                            \
+    const float dl = fminf(d[i], d[j]), dh = fmaxf(d[i], d[j]); \
+    const uint32_t el = sw ? e[j] : e[i], eh = sw ? e[i] : e[j]; \
+    d[i] = dl, d[j] = dh, e[i] = el, e[j] = eh;             \
+  }
+#else
 #define VXB_CSWAP(i, j)                       \
   if (d[j] < d[i]) {                          \
     float td = d[i]; d[i] = d[j]; d[j] = td;  \
     uint32_t te = e[i]; e[i] = e[j]; e[j] = te; \
   }
+#endif
   VXB_CSWAP(0, 1) VXB_CSWAP(2, 3) VXB_CSWAP(0, 2) VXB_CSWAP(1, 3) VXB_CSWAP(1, 2)
 #undef VXB_CSWAP
   if (d[0] < kInf) {
