@@ -19,13 +19,14 @@ def test_p2p_framebuffer_equals_nccl_gather():
         pytest.skip("needs 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29533", os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "2", "--warmup", "1",
-           "--workload", "cfg1_1080p_primary+shadow_100k", "--no-cpu"]
+           "--workload", "cfg1_1080p_primary+shadow_100k", "--no-cpu", "--scene-upload", "broadcast"]
     r = subprocess.run(cmd, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert line["n_gpus"] == 2
     assert line["config"]["p2p_frame_equals_nccl_gather_frame"] is True
     assert "peer memory" in line["config"]["framebuffer_transport"]
-    # the end-to-end leg replicates the scene by NCCL broadcast from rank 0 (+ vx_b200_mark_written): same frame
+    # the end-to-end leg replicates the scene by NCCL broadcast from rank 0 (+ vx_b200_mark_written; `auto` picks it from four GPUs
+    # up, so it is requested here): same frame
     assert line["config"]["e2e_frame_equals_checked_frame"] is True
     assert "broadcast" in line["config"]["scene_replication"]
