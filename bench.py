@@ -4,13 +4,29 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
-One "step" = one frame of the workload through vx_start (+ the NCCL framebuffer gather when N > 1).  Rank 0 prints ONE
-JSON line.  `value` = rays of all ranks / max-over-ranks device time, scene and framebuffer resident in HBM; `e2e` = the same
-frame through the reference-facing call sequence of the raycast host (vx_copy_to_dev of every scene buffer from pinned host
-memory, vx_upload_bytes(kernel_arg_t), vx_start, vx_ready_wait, vx_copy_from_dev of the framebuffer) timed on the host clock.
-`--impl reference` times the reference's own CPU implementation of the same frame (oracle/_ref = the reference sources
-compiled in place; the C port when that library did not travel) on all host threads.
-Workloads are BASELINE.json's configs; rays = every TLASIntersect-equivalent query (primary + shadow + bounce).
+ONE workload for every --gpus N (1 included): BASELINE configs[3], the 7680x4320 primary + shadow frame of the 1 002 528-triangle
+scene, so the N = 1/2/4/8 values form a strong-scaling curve.  One "step" = one frame through vx_start.  Multi-GPU is a
+property of the BACKEND: one process opens ONE vx_device_h that spans N GPUs (vx_b200_select_gpus / env
+VORTEX_B200_GPUS; slices of every upload over N PCIe links + NVLink replication, bands of the image per GPU, band-wise
+download), exactly what a Vortex host application gets.  Under torchrun rank 0 drives that device; the other ranks join the
+NCCL rendezvous and then wait (no GPU work of their own).  Rank 0 prints ONE JSON line:
+
+  value     rays of the step / device time of the step — CUDA events on GPU 0's stream, which records the begin event every
+            GPU waits for and joins every GPU's end event (vx_b200_stats_t.group_ms) — scene and framebuffer resident in HBM,
+            L2 flushed before every step;
+  e2e       the same frame through the raycast host's call sequence with HOST buffers every step: vx_copy_to_dev of the seven
+            scene buffers from pinned memory, vx_upload_bytes(kernel_arg_t), vx_start, vx_ready_wait, vx_copy_from_dev of the
+            framebuffer; host wall clock;
+  parity    the timed frame against the CPU checker (oracle/_ref = the reference's own sources, else the C port) on the very
+            bytes that were uploaded: 64 rows spread over the image pixel by pixel, and 2^18 primary rays as hit records;
+  roofline  what binds the kernel according to ncu (profiles/r02_ncu_metrics.json, captures of these workloads), with the live
+            kernel time: SIMT-adjusted issue utilisation, physical DRAM bytes/s against the HBM peak, algorithmic bytes of the
+            reference's order and of the kernel's own order;
+  config.secondary_workloads   BASELINE configs[2], the 4K primary frame, configs[1] (and configs[4] on 8 GPUs) measured the
+            same way (L2 flushed, >= 20 steps, own e2e / roofline / parity).
+
+`--impl reference` times the reference's own CPU implementation of the same frame (oracle/_ref compiled from the reference
+sources; the C port when that library did not travel) on all host threads.
 """
 import argparse
 import importlib
@@ -41,8 +57,11 @@ WORKLOADS = {
     "cfg4_incoherent_10m": dict(n=2237, w=8, h=8, mode=0, depth=1, config_index=4, rays_per_gpu=1 << 23, scale=4.0),
     "incoherent_1m": dict(n=708, w=8, h=8, mode=0, depth=1, config_index=None, rays_per_gpu=1 << 23),
 }
+DEFAULT_WORKLOAD = "cfg3_8k_primary+shadow_1m"
+SECONDARY = ("cfg2_4k_diffuse4_1m", "primary_4k_1m", "cfg1_1080p_primary+shadow_100k")
 METRIC = "Mrays/s (primary + shadow + bounce rays, whole job)"
 BAND_ROWS = 8
+NCU_METRICS = os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")
 
 
 def pkg(name):
@@ -59,15 +78,18 @@ def make_meshes(wl):
     return [m]
 
 
-def gather_roofline(dev, achieved_gbs, beyond_l2=False):
-    """second roofline denominator: random-record gather bandwidth into the SMs, measured live with the library's
-    probe kernel (vx_b200_probe_gather): 32-byte records = one reference box, 128-byte = one 4-wide record of the fast order.
-    The scratch buffer is L2-resident (32 MB) — or 1 GB, when the workload's scene is far beyond L2."""
-    size = (1 << 30) if beyond_l2 else (32 << 20)
-    p32, p128 = dev.probe_gather(size, 32), dev.probe_gather(size, 128)
-    return {"buffer_bytes": size, "resident_in": "HBM (buffer >> L2)" if beyond_l2 else "L2", "peak_32B_records": p32, "peak_128B_records": p128,
-            "unit": "GB/s", "achieved": achieved_gbs, "frac": achieved_gbs / p32 if p32 > 0 else None,
-            "note": "achieved = the same algorithmic bytes/s as roofline.achieved, against the 32-byte-record gather rate"}
+_HOST_SCENES = {}
+
+
+def host_scene(wl):
+    """the product's own host builders (reference byte layouts), one build per geometry"""
+    key = (wl["n"], wl.get("scale", 1.0))
+    if key not in _HOST_SCENES:
+        t0 = time.perf_counter()
+        hs = pkg("host").HostScene(make_meshes(wl))
+        _HOST_SCENES.clear()            # one 10 M-triangle scene is 1.6 GB of host arrays: keep only the latest
+        _HOST_SCENES[key] = (hs, time.perf_counter() - t0)
+    return _HOST_SCENES[key]
 
 
 def peaks():
@@ -78,16 +100,23 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
 
 
+def ncu_metrics(name):
+    try:
+        return json.load(open(NCU_METRICS)).get(name)
+    except Exception:
+        return None
+
+
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled while the timed region runs (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks + throttle reasons sampled while the timed region runs (B200_PROFILING.md recipe), all GPUs in use."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
+    def __init__(self, indices):
         self.rows, self.proc = [], None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                                          ",".join(str(i) for i in indices)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -116,12 +145,19 @@ class ClockSampler:
 
 def rt_unit_perf(st, order):
     """RT-unit style counters of one run (SURVEY 8f-4; the shape of RTUnit::PerfStats, sim/simx/rt_unit.h:15-45) in traversal
-    steps instead of simulated cycles: a step = one node fetch + its box tests, or one leaf."""
+    steps / lane-iterations instead of simulated cycles."""
     if not st.get("warp_steps"):
         return None
-    return {"order": order, "warps": st["warps"], "warp_steps": st["warp_steps"], "thread_steps": st["lane_steps"],
-            "simt_efficiency": st["lane_steps"] / (32.0 * st["warp_steps"]),
-            "thread_steps_per_ray": st["lane_steps"] / max(1, st["rays"])}
+    out = {"order": order, "warps": st["warps"], "warp_steps": st["warp_steps"], "thread_steps": st["lane_steps"],
+           "simt_efficiency": st["lane_steps"] / (32.0 * st["warp_steps"]),
+           "thread_steps_per_ray": st["lane_steps"] / max(1, st["rays"])}
+    if any(any(r) for r in st.get("latency_dist", [])):
+        out["latency_dist"] = {"rows": ["warp fetching work (GEN)", "warp shading (POST)", "warp traversing (TRAV)"],
+                               "cols": ["awaiting_processing", "awaiting_scheduling", "awaiting_mf", "executing_op", "trace_complete"],
+                               "lane_iterations": st["latency_dist"]}
+    if any(st.get("steps_hist", [])):
+        out["steps_per_ray_hist_log2"] = st["steps_hist"]
+    return out
 
 
 def algorithmic_work(st, pixels):
@@ -129,6 +165,49 @@ def algorithmic_work(st, pixels):
     b = 32 * st["box_tests"] + 40 * st["tri_tests"] + 160 * st["blas_entered"] + (60 + 160 + 4) * st["shaded_hits"] + 4 * pixels
     f = 27 * st["box_tests"] + 53 * st["tri_tests"] + 30 * st["blas_entered"] + 80 * st["shaded_hits"]
     return b, f
+
+
+def own_work(st, pixels, ray_io_bytes=0):
+    """bytes the KERNEL's own (fast) order asks the memory system for: one 128-byte 4-wide record per four box tests, a 48-byte
+    edge-form triangle per test, 48 bytes of instance transform per entry, the shading records, the pixel (or ray + hit record)"""
+    return (128 * (st["box_tests"] // 4) + 48 * st["tri_tests"] + 48 * st["blas_entered"] + (60 + 160 + 4) * st["shaded_hits"]
+            + 4 * pixels + ray_io_bytes)
+
+
+def roofline_block(name, kernel, k_ms, n_gpus, work_ref, work_own, abytes, aflops, own_bytes, nsm_total):
+    """What binds the kernel (ncu capture of THIS workload, profiles/r02_ncu_metrics.json) scaled by the live kernel time."""
+    hbm, hbm_src, sm_mhz = peaks()
+    m = ncu_metrics(name)
+    sec = k_ms * 1e-3
+    fp32_peak = nsm_total * 128 * 2 * sm_mhz * 1e6 / 1e12
+    issue_peak = nsm_total * 4 * 32 * sm_mhz * 1e6 / 1e9            # G thread-instructions/s: 4 schedulers x 32 lanes per SM and clock
+    out = {"kernel": kernel, "kernel_ms": k_ms, "peak_source": hbm_src,
+           "algorithmic": {"reference_order_bytes_per_launch": abytes, "reference_order_gbs": abytes / sec / 1e9,
+                           "kernel_order_bytes_per_launch": own_bytes, "kernel_order_gbs": own_bytes / sec / 1e9,
+                           "bytes_per_ray_reference_order": abytes / max(1, work_ref["rays"]),
+                           "bytes_per_ray_kernel_order": own_bytes / max(1, work_own["rays"]),
+                           "note": "SURVEY 8(d) formula on the strict-order counters (= the reference's own walk) and on the fast "
+                                   "order's own fetches (4-wide records); served mostly from L1/L2, so neither is an HBM fraction"},
+           "fp32": {"achieved_tflops": aflops / sec / 1e12, "peak_tflops": fp32_peak, "frac": aflops / sec / 1e12 / fp32_peak},
+           "work_per_ray": {"reference_order": {k: work_ref[k] / max(1, work_ref["rays"]) for k in ("box_tests", "tri_tests", "blas_entered", "shaded_hits")},
+                            "kernel_order": {k: work_own[k] / max(1, work_own["rays"]) for k in ("box_tests", "tri_tests", "blas_entered", "shaded_hits")}}}
+    if not m:
+        out.update({"bound": "issue", "achieved": None, "peak": issue_peak, "unit": "G thread-instructions/s", "frac": None, "traffic": None,
+                    "note": "no ncu capture of this workload at this commit (profiles/r02_ncu_metrics.json)"})
+        return out
+    g = max(1, n_gpus)
+    thread_inst = m["thread_inst_executed"] / (m.get("gpus", 1)) * g if m.get("scale_with_gpus") else m["thread_inst_executed"]
+    achieved = thread_inst / sec / 1e9
+    dram = m["dram_bytes"]
+    out.update({"bound": m.get("bound", "issue"), "achieved": achieved, "peak": issue_peak, "unit": "G thread-instructions/s",
+                "frac": achieved / issue_peak, "traffic": dram,
+                "hbm": {"achieved_gbs": dram / sec / 1e9, "peak_gbs": hbm * g, "frac": dram / sec / 1e9 / (hbm * g)},
+                "ncu": {k: m[k] for k in m if k not in ("thread_inst_executed", "dram_bytes")}, "ncu_file": m.get("file"),
+                "note": "achieved = thread-instructions per launch (ncu smsp__thread_inst_executed.sum of this workload) / live kernel "
+                        "time; peak = SMs x 4 schedulers x 32 lanes x SM clock; frac = issue-slot utilisation x SIMT efficiency. "
+                        "`traffic` = DRAM bytes per launch from the same capture; `hbm.frac` = those bytes / live time / measured HBM "
+                        "peak.  The work per launch is fixed by the workload (total over the GPUs), the time is this run's."})
+    return out
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -143,12 +222,9 @@ def cpu_oracle():
     return po.PortRaycast(), "port"
 
 
-def cpu_frame_timer(wl, budget_s):
-    """returns (fn() -> (seconds, rays), description).  The sample is the whole frame unless one frame would blow the budget,
-    in which case a centred band of rows (multiple of 8) is timed instead."""
-    orc, kind = cpu_oracle()
-    sc = orc.scene_create(make_meshes(wl))
-    sc.setup(wl["w"], wl["h"], spp=1, max_depth=wl["depth"])
+def cpu_frame_timer(sc, orc, kind, wl, budget_s):
+    """returns (fn() -> (seconds, rays), kind, threads, description).  The sample is the whole frame unless one frame would blow
+    the budget, in which case a centred band of rows (multiple of 8) is timed instead."""
     threads = orc.hw_threads()
     H = wl["h"]
     probe_rows = (H // 2 // 8 * 8, min(H, H // 2 // 8 * 8 + 8))
@@ -190,10 +266,10 @@ def run_reference(args, wl, name):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    orc, kind = cpu_oracle()
+    sc = orc.scene_create(make_meshes(wl))          # the reference's own Scene / BVH builders
+    sc.setup(wl["w"], wl["h"], spp=1, max_depth=wl["depth"])
     if "rays_per_gpu" in wl:      # incoherent-ray workload: the reference's TLASIntersect over a bounded sample of the same ray set
-        orc, kind = cpu_oracle()
-        sc = orc.scene_create(make_meshes(wl))
-        sc.setup(wl["w"], wl["h"], spp=1, max_depth=1)
         threads = orc.hw_threads()
         n_s = 1 << 18
         sc_ = np.float32(wl.get("scale", 1.0))
@@ -206,7 +282,7 @@ def run_reference(args, wl, name):
             return time.perf_counter() - t, n_s
         sample = f"first {n_s} rays of the global ray set, all host threads"
     else:
-        frame, kind, threads, sample = cpu_frame_timer(wl, budget_s=max(2.0, 150.0 / max(1, args.steps + args.warmup)))
+        frame, kind, threads, sample = cpu_frame_timer(sc, orc, kind, wl, budget_s=max(2.0, 150.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         frame()
     tot_t, tot_r = 0.0, 0
@@ -216,8 +292,8 @@ def run_reference(args, wl, name):
         tot_r += n
     v = tot_r / tot_t / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True, "scaling": "weak" if "rays_per_gpu" in wl else "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": name, "width": wl["w"], "height": wl["h"], "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32,
                        "mode": wl["mode"], "max_depth": wl["depth"]},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
@@ -228,450 +304,309 @@ def run_reference(args, wl, name):
 # ------------------------------------------------------------------------------------------------------------------
 # the b200 arm
 # ------------------------------------------------------------------------------------------------------------------
-def run_b200(args, wl, name):
-    import torch
-    import torch.distributed as dist
+def sample_bands(H, n_gpus, n_bands=8):
+    """8-row bands spread over the image whose indices fall on different GPUs of the round-robin deal"""
+    nb = H // BAND_ROWS
+    if nb <= n_bands:
+        return list(range(nb))
+    out = []
+    for k in range(n_bands):
+        b = (k * nb) // n_bands + (k % max(1, n_gpus))
+        out.append(min(nb - 1, b))
+    return sorted(set(out))
 
-    vx, tracer_mod, host, mg = pkg("vx"), pkg("tracer"), pkg("host"), pkg("multigpu")
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py --impl b200 needs a CUDA device: the b200 backend has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    W, H = wl["w"], wl["h"]
 
-    # ---- host side: scene preparation with the product's own builders (reference byte layouts) ----
+def parity_frames(tr, wl, bufs, karg, frame, n_gpus, max_rays=1 << 18, order="fast (the timed configuration)"):
+    """the frame that was timed against the CPU checker run on the very bytes that were uploaded (raycast/tracer.cpp:249-263 is
+    the loop the checker runs; north_star gates).  Pixels: 64 rows spread over the image.  Hit records: primary rays of those
+    rows (at most 2^18), the same rays given to vx_b200_trace_rays and to the checker's TLASIntersect."""
+    po = importlib.import_module("oracle.pyoracle")
+    par = pkg("parity")
+    orc, kind = cpu_oracle()
+    raw = po.RawScene(orc, bufs, karg)
+    threads = orc.hw_threads()
+    bands = sample_bands(wl["h"], n_gpus)
     t0 = time.perf_counter()
-    hs = host.HostScene(make_meshes(wl))
+    differ, maxd, npix = 0, 0, 0
+    for b in bands:
+        rows = (b * BAND_ROWS, min(wl["h"], (b + 1) * BAND_ROWS))
+        ref, _ = raw.render(mode=wl["mode"], rows=rows, threads=threads)
+        g, r = frame[rows[0]:rows[1]], ref[rows[0]:rows[1]]
+        differ += int((g != r).sum())
+        maxd = max(maxd, par.channel_diff(g, r))
+        npix += g.size
+    ys = [y for b in bands for y in range(b * BAND_ROWS, min(wl["h"], (b + 1) * BAND_ROWS))]
+    rays = par.primary_rays(karg, ys)
+    if len(rays) > max_rays:
+        rays = np.ascontiguousarray(rays[:: (len(rays) + max_rays - 1) // max_rays])
+    hp = par.hit_parity(tr.trace_rays(rays), raw.trace_rays(rays, threads=threads))
+    return {"checker": kind, "checked_order": order, "rows": len(ys), "bands": bands, "pixels": npix,
+            "pixels_differ": differ, "max_channel_diff": maxd, "rays": hp["n"], "id_mismatch": hp["mismatch"], "ties": hp["ties"],
+            "non_tie": hp["non_tie"], "max_rel_t": hp["max_rel_t"], "bit_exact_t": hp["bit_exact_t"], "mismatch_frac": hp["mismatch_frac"],
+            "gates": "ids equal on >= 99.99 % of rays, every residual mismatch an equal-t tie; t within 1e-5 relative; colour within 1/255",
+            "green": bool(hp["non_tie"] == 0 and hp["mismatch_frac"] <= 1e-4 and hp["max_rel_t"] <= 1e-5 and maxd <= 1),
+            "seconds": round(time.perf_counter() - t0, 2)}
+
+
+def measure_frames(name, gpus, steps, warmup, kernel=0, cpu=False, parity=True, clocks=False):
+    """one frame workload on one vx device over `gpus` GPUs: kernel-side value, e2e, roofline, parity"""
+    import torch
+
+    tracer_mod = pkg("tracer")
+    wl = WORKLOADS[name]
+    W, H = wl["w"], wl["h"]
+    hs, build_s = host_scene(wl)
     karg = hs.setup(W, H, spp=1, max_depth=wl["depth"])
     bufs = hs.buffers()
-    build_s = time.perf_counter() - t0
-
-    tr = tracer_mod.Tracer(W, H, 1, wl["depth"], cuda_device=local).init(bufs)
+    tr = tracer_mod.Tracer(W, H, 1, wl["depth"], cuda_device=0, gpus=gpus).init(bufs)
     tr.setup({k: karg[k][0] for k in karg.dtype.names})
-    tr.dev.set_partition(rank, world, BAND_ROWS)
-    tr.set_mode(wl["mode"], 0, kernel=args.kernel)
+    tr.set_mode(wl["mode"], 0, kernel=kernel)
     tr._upload_args()
-    ext = torch.cuda.ExternalStream(tr.dev.stream(), device=torch.device("cuda", local))
-    fb = mg.framebuffer_tensor(tr, local)
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")       # > 126 MB L2
+    dev = tr.dev
+    warmup = max(4, warmup)          # the schedule trial (row-major vs recorded-cost order) takes frames 0-3
 
-    # N > 1: by default the ranks' kernels store their bands straight into rank 0's framebuffer over NVLink peer memory
-    # (--gather p2p); --gather nccl renders locally and moves the bands with one NCCL gather inside the timed region.
-    p2p = world > 1 and args.gather == "p2p"
-    check = {}
-    if world > 1:   # both transports must deliver the same frame to rank 0
-        tr.dev.start(tr.krnl, tr.args)
-        with torch.cuda.stream(ext):
-            mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
-        ext.synchronize()
-        tr.dev.ready_wait()
-        ref_frame = fb.clone() if rank == 0 else None
-        if rank == 0:
-            fb.zero_()
-        torch.cuda.synchronize()
-        dist.barrier()
-        mg.share_framebuffer(tr, rank, world)
-        tr.dev.start(tr.krnl, tr.args)
-        tr.dev.ready_wait()
-        torch.cuda.synchronize()
-        dist.barrier()
-        if rank == 0:
-            check["p2p_frame_equals_nccl_gather_frame"] = bool(torch.equal(fb, ref_frame))
-        if not p2p:
-            mg.unshare_framebuffer(tr, rank, world)
+    def timed(n, warm):
+        for _ in range(warm):
+            dev.flush_l2()
+            dev.start(tr.krnl, tr.args)
+            dev.ready_wait()
+        out = []
+        for _ in range(n):
+            dev.flush_l2()                          # L2 flush on every GPU, before the step's begin event
+            dev.start(tr.krnl, tr.args)
+            dev.ready_wait()
+            st = dev.stats()
+            out.append((st["group_ms"], st["kernel_ms"], st["kernel_ms_min"]))
+        return out, dev.stats()
 
-    def step(timed_events=None):
-        with torch.cuda.stream(ext):
-            flush.zero_()                                       # L2 flush between iterations, outside the timed pair
-            if timed_events:
-                timed_events[0].record()
-            tr.dev.start(tr.krnl, tr.args)                      # vx_start: async, on the same CUDA stream
-            if world > 1 and not p2p:
-                mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
-            if timed_events:
-                timed_events[1].record()
-
-    def sync_all():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        step()
-    sync_all()
-    tr.dev.ready_wait()
-    sampler = ClockSampler(local) if rank == 0 else None
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms = []
-    for e in evs:
-        step(e)
-        tr.dev.ready_wait()
-        kernel_ms.append(tr.dev.last_kernel_ms())
-    sync_all()
-    clocks = sampler.stop() if sampler else None
-    total_ms = sum(a.elapsed_time(b) for a, b in evs)
-    st = tr.dev.stats()
-    rays_rank = st["rays"]
-    launches_per_step = st["kernel_launches"]
-    t_ms = torch.tensor([total_ms], dtype=torch.float64, device=f"cuda:{local}")
-    r_cnt = torch.tensor([rays_rank], dtype=torch.int64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(r_cnt, op=dist.ReduceOp.SUM)
-    total_ms, rays_step = float(t_ms.item()), int(r_cnt.item())
-    value = rays_step * args.steps / (total_ms * 1e3)
+    # schedule feedback off = what the first frame of a new view costs (row-major tile order)
+    os.environ["VORTEX_B200_SCHEDULE"] = "0"
+    off, st_off = timed(max(3, min(steps, 10)), 3)
+    os.environ.pop("VORTEX_B200_SCHEDULE", None)
+    sampler = ClockSampler(list(range(gpus))) if clocks else None
+    runs, st = timed(steps, warmup)
+    clk = sampler.stop() if sampler else None
+    rays_step = st["rays"]
+    total_ms = sum(r[0] for r in runs)
+    value = rays_step * steps / (total_ms * 1e3)
+    k_ms = float(np.mean([r[1] for r in runs]))
+    feedback_off = {"value": st_off["rays"] * len(off) / (sum(r[0] for r in off) * 1e3), "unit": "Mrays/s", "steps": len(off),
+                    "note": "VORTEX_B200_SCHEDULE=0: tiles handed out row-major, i.e. the first frame of a new view"}
 
     # ---- e2e: the raycast host's call sequence with HOST buffers, every step ----
     pinned = {n: torch.from_numpy(bufs[n].copy()).pin_memory() for n in tracer_mod.SCENE_BUFFERS if bufs[n].nbytes}
     out_pinned = torch.empty((H, W), dtype=torch.int32).pin_memory()
     h2d = sum(t.numel() for t in pinned.values()) + 192
-    d2h = W * H * 4 if rank == 0 else 0
-
-    # N > 1: the scene enters the box once — rank 0 uploads it from its host buffers and the other ranks receive it over NVLink
-    # (NCCL broadcast into their own vx buffers + vx_b200_mark_written) instead of N uploads through the host's memory system
-    bcast = world > 1 and (args.scene_upload == "broadcast" or (args.scene_upload == "auto" and world >= 4))
-    scene_t = mg.scene_tensors(tr, local) if bcast else None
+    d2h = W * H * 4
 
     def e2e_step():
-        if not bcast or rank == 0:
-            for n, t in pinned.items():
-                tr.bufs[n].copy_to_dev((t.data_ptr(), t.numel()))
-        if bcast:
-            with torch.cuda.stream(ext):
-                mg.broadcast_scene(tr, scene_t, rank, world)
-            ext.synchronize()
+        for n, t in pinned.items():
+            tr.bufs[n].copy_to_dev((t.data_ptr(), t.numel()))
         tr._upload_args()
-        tr.dev.start(tr.krnl, tr.args)
-        if world > 1 and not p2p:
-            with torch.cuda.stream(ext):
-                mg.gather_framebuffer(fb, rank, world, BAND_ROWS)
-            ext.synchronize()
-        tr.dev.ready_wait()
-        if p2p:
-            dist.barrier()          # every rank's bands have landed in rank 0's framebuffer
-        if rank == 0:
-            tr.out.copy_from_dev((out_pinned.data_ptr(), W * H * 4))
+        dev.start(tr.krnl, tr.args)
+        dev.ready_wait()
+        tr.out.copy_from_dev((out_pinned.data_ptr(), d2h))
 
-    # warm-up of the end-to-end sequence: the first host->device copies of a process run at ~14 GB/s and reach the link rate
-    # (~50 GB/s) only after the GPU has seen some tens of ms of work (tools/quick_upload_probe2.py, profiles/r01_upload_ramp.txt),
-    # so the untimed steps cover that ramp: at least W steps and at least 0.15 s, the same count on every rank
-    e2e_steps = max(3, min(args.steps, 20))
-    e2e_warm = max(3, args.warmup)
-    t_w = time.perf_counter()
-    for _ in range(e2e_warm):
-        e2e_step()
-    sync_all()
-    per_step = max((time.perf_counter() - t_w) / e2e_warm, 1e-4)
-    more = torch.tensor([min(200, max(0, int(0.15 / per_step) - e2e_warm))], dtype=torch.int64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(more, op=dist.ReduceOp.MAX)
-    for _ in range(int(more.item())):
-        e2e_step()
-    e2e_warm += int(more.item())
-    sync_all()
-    e2e_batches = []            # three timed batches of e2e_steps frames; the line carries the median batch (host timing jitters)
-    for _ in range(3):
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
+    def e2e_measure(n_steps):
+        # warm-up: the first host->device copies of a process run at ~14 GB/s and reach the link rate only after the GPU has seen
+        # some tens of ms of work (profiles/r01_upload_ramp.txt): at least 3 steps and 0.15 s
+        t_w, n_w = time.perf_counter(), 0
+        while n_w < 3 or (time.perf_counter() - t_w < 0.15 and n_w < 200):
             e2e_step()
-        sync_all()
-        e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local}")
-        if world > 1:
-            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        e2e_batches.append(rays_step * e2e_steps / float(e2e_s.item()) / 1e6)
-    e2e_value = sorted(e2e_batches)[1]
-    e2e_launches = tr.dev.stats()["kernel_launches"]
-    if world > 1 and rank == 0:   # the frame that came out of the end-to-end sequence is the frame of the transport check
-        check["e2e_frame_equals_checked_frame"] = bool(np.array_equal(out_pinned.numpy().view(np.uint32), ref_frame.cpu().numpy().view(np.uint32)))
-        check["scene_replication"] = ("rank 0 uploads, NCCL broadcast over NVLink to the other ranks' vx buffers" if bcast
-                                      else "every rank uploads its own copy")
+            n_w += 1
+        batches = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            for _ in range(n_steps):
+                e2e_step()
+            batches.append(rays_step * n_steps / (time.perf_counter() - t0) / 1e6)
+        return sorted(batches)[1], batches, n_w
 
-    # ---- roofline of the dominant kernel (k_render_a): algorithmic bytes of the reference algorithm / kernel time ----
-    tr.set_mode(wl["mode"], 1)              # strict order = the reference's own visiting order => its algorithmic work
-    tr.dev.enable_stats(True)
-    tr._upload_args()
+    e2e_steps = max(3, min(steps, 20))
+    e2e_plain, plain_batches, e2e_warm = e2e_measure(e2e_steps)
+    frame_plain = out_pinned.numpy().view(np.uint32).copy()
+    dev.set_readback(tr.out, out_pinned.data_ptr(), d2h)          # the image follows the kernels into host memory, band by band
+    out_pinned.zero_()
+    e2e_rb, rb_batches, _ = e2e_measure(e2e_steps)
+    frame_rb = out_pinned.numpy().view(np.uint32).copy()
+    dev.set_readback(tr.out, None, 0)
+    e2e_launches = dev.stats()["kernel_launches"]
+    use_rb = e2e_rb > e2e_plain
+    e2e = {"value": max(e2e_rb, e2e_plain), "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+           "warmup": e2e_warm, "batches": rb_batches if use_rb else plain_batches,
+           "sequence": "7 x vx_copy_to_dev (pinned host scene buffers) + vx_upload_bytes(kernel_arg_t) + vx_start + vx_ready_wait + "
+                       "vx_copy_from_dev(framebuffer -> pinned host image)" + (", with vx_b200_set_readback registered once before the loop "
+                       "(the framebuffer copy is issued behind the kernels on each GPU's stream)" if use_rb else ""),
+           "plain_sequence": {"value": e2e_plain, "batches": plain_batches},
+           "with_readback": {"value": e2e_rb, "batches": rb_batches, "same_frame": bool(np.array_equal(frame_rb, frame_plain))},
+           "timer": "host wall clock around the synchronous vx_* calls", "launches_per_step": e2e_launches}
+
+    # ---- work counters: strict order = the reference's own walk; fast order = what the timed kernel does ----
+    dev.enable_stats(True)
+    tr.set_mode(wl["mode"], 1)
     tr.launch()
-    work = tr.dev.stats()
-    tr.set_mode(wl["mode"], 0)
+    work_ref = dev.stats()
+    tr.set_mode(wl["mode"], 0, kernel=kernel)
     tr.launch()
-    unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(work, "strict")]
-    tr.dev.enable_stats(False)
-    pixels_rank = len(mg.owned_rows(rank, world, H, BAND_ROWS)) * W
-    abytes, aflops = algorithmic_work(work, pixels_rank)
-    k_ms = float(np.mean(kernel_ms))
-    hbm, hbm_src, sm_mhz = peaks()
-    achieved = abytes / (k_ms * 1e-3) / 1e9
-    nsm = tr.dev.caps(0x3)
-    fp32_peak = nsm * 128 * 2 * sm_mhz * 1e6 / 1e12
-    gather = gather_roofline(tr.dev, achieved) if rank == 0 else None
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        try:
-            traffic = json.load(open(tpath)).get(name)
-        except Exception:
-            traffic = None
+    work_own = dev.stats()
+    dev.enable_stats(False)
+    unit_perf = [rt_unit_perf(work_own, "fast"), rt_unit_perf(work_ref, "strict")]
+    abytes, aflops = algorithmic_work(work_ref, W * H)
+    roof = roofline_block(name, "k_render_a" if kernel == 1 else "k_render_m", k_ms, gpus, work_ref, work_own, abytes, aflops,
+                          own_work(work_own, W * H), dev.caps(0x3))
 
-    extra = {}
-    if rank == 0 and world == 1 and args.extra:
-        tr.close()
-        tr = None
-        for other in ("primary_4k_1m", "cfg2_4k_diffuse4_1m", "cfg3_8k_primary+shadow_1m"):
-            if other != name:
-                extra[other] = quick_run(other, local, kernel=args.kernel)
-        if "cfg3_8k_primary+shadow_1m" in extra:   # --gpus N > 1 runs BASELINE configs[3] (strong scaling); this is its one-GPU point
-            extra["cfg3_8k_primary+shadow_1m"]["note"] += "; the one-GPU base of the strong-scaling series that --gpus 2/4/8 measure"
-        extra["rtu_1080p_primary_100k"] = quick_run_rtu(local, with_cpu=not args.no_cpu)
+    par = None
+    if parity:
+        tr.set_mode(wl["mode"], 0, kernel=kernel)
+        frame = tr.run()
+        par = parity_frames(tr, wl, bufs, karg, frame, gpus)
+        par["e2e_frame_equals_timed_frame"] = bool(np.array_equal(frame_plain, frame))
 
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        frame, kind, threads, sample = cpu_frame_timer(wl, budget_s=20.0)
+    cpu_b = None
+    if cpu:
+        po = importlib.import_module("oracle.pyoracle")
+        orc, kind = cpu_oracle()
+        raw = po.RawScene(orc, bufs, karg)        # the reference's hot loop on the very bytes that were uploaded
+        fr, kind, threads, sample = cpu_frame_timer(raw, orc, kind, wl, budget_s=12.0)
         best = None
         for _ in range(2):
-            dt, n = frame()
+            dt, n = fr()
             best = (dt, n) if best is None or dt < best[0] else best
-        cpu = {"value": best[1] / best[0] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample + ", best of 2"}
-        cpu["single_thread"] = frame.single()
-
-    if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic",
-                "config": {"workload": name, "baseline_config_index": wl["config_index"], "width": W, "height": H,
-                           "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32, "mode": wl["mode"], "max_depth": wl["depth"],
-                           "rays_per_step": rays_step, "partition": f"{BAND_ROWS}-row bands round-robin over {world} GPU(s), scene replicated",
-                           "schedule_feedback": "on: tile groups handed out in descending order of the cost recorded on earlier frames when "
-                                                "a timed trial during warm-up found that faster (DESIGN 5; VORTEX_B200_SCHEDULE=0 disables)",
-                           "framebuffer_transport": ("none (single GPU)" if world == 1 else
-                                                     "kernels store into rank 0's framebuffer over NVLink peer memory (CUDA IPC)" if p2p else
-                                                     "NCCL gather inside the timed region"), **check,
-                           "l2": "512 MB memset between timed iterations (L2 flush); timed per step with CUDA events on the launch stream",
-                           "host_bvh_build_s": round(build_s, 3), "extra_workloads": extra},
-                "clocks": clocks,
-                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "warmup": e2e_warm, "batches": e2e_batches,
-                        "timer": "host wall clock around the synchronous vx_* calls, max over ranks", "launches_per_step": e2e_launches},
-                "gpu_launches": int(launches_per_step) * args.steps, "rt_unit_perf": unit_perf,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
-                             "peak_source": hbm_src, "kernel": "k_render_a" if args.kernel == 1 else "k_render_m", "kernel_ms": k_ms,
-                             "algorithmic_bytes_per_launch": abytes, "algorithmic_bytes_per_ray": abytes / max(1, work["rays"]),
-                             "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
-                                      "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},
-                             "work_per_ray": {k: work[k] / max(1, work["rays"]) for k in ("box_tests", "tri_tests", "blas_entered", "shaded_hits")},
-                             "l2_gather": gather,
-                             "note": "achieved = the REFERENCE algorithm's bytes for the counted work (strict-order counters) / kernel time, as "
-                                     "the contract defines it; those bytes are served from L1/L2 (`traffic` is what reached DRAM) and the "
-                                     "4-wide records read fewer of them, so frac can exceed 1 — the binding resource is instruction issue "
-                                     "(ncu: 80 % issue-active, profiles/r01_ncu_machine_cfg1_sched.txt)"},
-                "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
-    if tr is not None:
-        tr.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        cpu_b = {"value": best[1] / best[0] / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample + ", best of 2"}
+        cpu_b["single_thread"] = fr.single()
+    launches = int(st["kernel_launches"])
+    tr.close()
+    return {"workload": name, "baseline_config_index": wl["config_index"], "value": value, "unit": "Mrays/s", "n_gpus": gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": total_ms / steps, "rays_per_step": rays_step, "width": W, "height": H,
+            "triangles": 2 * wl["n"] ** 2 if wl["n"] else 32, "mode": wl["mode"], "max_depth": wl["depth"],
+            "per_gpu_kernel_ms": {"slowest": k_ms, "fastest": float(np.mean([r[2] for r in runs]))},
+            "schedule_feedback_off": feedback_off, "e2e": e2e, "gpu_launches": launches * steps, "rt_unit_perf": unit_perf,
+            "roofline": roof, "parity": par, "cpu_baseline": cpu_b, "clocks": clk, "host_bvh_build_s": round(build_s, 3)}
 
 
-def run_incoherent(args, wl, name):
-    """BASELINE configs[4]: closest-hit records of incoherent rays through vx_b200_trace_rays.  Rays are sharded by
-    index (rank r traces rays [r*R, (r+1)*R) of one global WangHash-seeded set), the scene is replicated, no data-path collective:
-    weak scaling.  value = rays of all ranks / max-over-ranks device time with rays and scene resident in HBM; e2e adds the
-    host->device copy of the rays and the device->host copy of the hit records every step."""
+def measure_incoherent(name, gpus, steps, warmup, cpu=False, clocks=False):
+    """BASELINE configs[4]: closest-hit records of incoherent rays through vx_b200_trace_rays.  One global
+    WangHash-seeded ray set of 2^23 rays per GPU, sharded by index over the GPUs of the device (scene replicated, no data-path
+    collective: weak scaling).  e2e = vx_b200_trace_rays_host: pinned host rays in, pinned host hit records out."""
     import torch
-    import torch.distributed as dist
 
-    vx, tracer_mod, host, scenes = pkg("vx"), pkg("tracer"), pkg("host"), pkg("scenes")
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py --impl b200 needs a CUDA device: the b200 backend has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    R = int(wl["rays_per_gpu"])
-    t0 = time.perf_counter()
-    hs = host.HostScene(make_meshes(wl))
+    tracer_mod, scenes = pkg("tracer"), pkg("scenes")
+    wl = WORKLOADS[name]
+    R = int(wl["rays_per_gpu"]) * gpus
+    hs, build_s = host_scene(wl)
     karg = hs.setup(wl["w"], wl["h"], spp=1, max_depth=1)
     bufs = hs.buffers()
-    build_s = time.perf_counter() - t0
-    tr = tracer_mod.Tracer(wl["w"], wl["h"], 1, 1, cuda_device=local).init(bufs)
+    tr = tracer_mod.Tracer(wl["w"], wl["h"], 1, 1, cuda_device=0, gpus=gpus).init(bufs)
     tr.setup({k: karg[k][0] for k in karg.dtype.names})
     tr.set_mode(0, 0)
     tr._upload_args()
+    dev = tr.dev
     sc_ = np.float32(wl.get("scale", 1.0))
     rays = scenes.random_rays(R, tuple(sc_ * np.float32(v) for v in (-1.0, -0.05, -1.0)), tuple(sc_ * np.float32(v) for v in (1.0, 0.45, 1.0)),
-                              seed=1, start=rank * R)   # the scene's AABB, a little headroom above
+                              seed=1, start=0)   # the scene's AABB, a little headroom above
     rays_pinned = torch.from_numpy(rays).pin_memory()
     hits_pinned = torch.empty(R * 24, dtype=torch.uint8).pin_memory()
-    rb = tr.dev.mem_alloc(R * 24)
-    hb = tr.dev.mem_alloc(R * 24)
+    rb = dev.mem_alloc(R * 24)
+    hb = dev.mem_alloc(R * 24)
     rb.copy_to_dev((rays_pinned.data_ptr(), R * 24))
-    ext = torch.cuda.ExternalStream(tr.dev.stream(), device=torch.device("cuda", local))
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device=f"cuda:{local}")
+    warmup = max(3, warmup)
+    for _ in range(warmup):
+        dev.flush_l2()
+        dev.trace_rays(tr.args, rb, R, hb)
+        dev.ready_wait()
+    sampler = ClockSampler(list(range(gpus))) if clocks else None
+    runs = []
+    for _ in range(steps):
+        dev.flush_l2()
+        dev.trace_rays(tr.args, rb, R, hb)
+        dev.ready_wait()
+        st = dev.stats()
+        runs.append((st["group_ms"], st["kernel_ms"], st["kernel_ms_min"]))
+    clk = sampler.stop() if sampler else None
+    launches = int(dev.stats()["kernel_launches"])
+    total_ms = sum(r[0] for r in runs)
+    value = R * steps / (total_ms * 1e3)
+    k_ms = float(np.mean([r[1] for r in runs]))
 
-    def step(ev=None):
-        with torch.cuda.stream(ext):
-            flush.zero_()
-            if ev:
-                ev[0].record()
-            tr.dev.trace_rays(tr.args, rb, R, hb)
-            if ev:
-                ev[1].record()
-
-    def sync_all():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        step()
-    sync_all()
-    tr.dev.ready_wait()
-    sampler = ClockSampler(local) if rank == 0 else None
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms = []
-    for e in evs:
-        step(e)
-        tr.dev.ready_wait()
-        kernel_ms.append(tr.dev.last_kernel_ms())
-    sync_all()
-    clocks = sampler.stop() if sampler else None
-    total_ms = sum(a.elapsed_time(b) for a, b in evs)
-    launches_per_step = tr.dev.stats()["kernel_launches"]
-    t_ms = torch.tensor([total_ms], dtype=torch.float64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-    total_ms = float(t_ms.item())
-    rays_step = R * world
-    value = rays_step * args.steps / (total_ms * 1e3)
-
-    def e2e_step_calls():      # the four reference-shaped calls, one after the other
+    def e2e_calls():           # the four reference-shaped calls, one after the other
         rb.copy_to_dev((rays_pinned.data_ptr(), R * 24))
-        tr.dev.trace_rays(tr.args, rb, R, hb)
-        tr.dev.ready_wait()
+        dev.trace_rays(tr.args, rb, R, hb)
+        dev.ready_wait()
         hb.copy_from_dev((hits_pinned.data_ptr(), R * 24))
 
-    def e2e_step():            # the host-buffer entry point: same records, upload / traversal / download of chunks overlapped
-        tr.dev.trace_rays_host(tr.args, rays_pinned.data_ptr(), R, hits_pinned.data_ptr())
+    def e2e_host():            # the host-buffer entry point: same records, upload / traversal / download of chunks overlapped
+        dev.trace_rays_host(tr.args, rays_pinned.data_ptr(), R, hits_pinned.data_ptr())
 
     def e2e_measure(fn, n):
         fn()
-        sync_all()
         t0 = time.perf_counter()
         for _ in range(n):
             fn()
-        sync_all()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local}")
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        return rays_step * n / float(dt.item()) / 1e6
+        return R * n / (time.perf_counter() - t0) / 1e6
 
-    e2e_steps = max(3, min(args.steps, 5))
-    e2e_calls_value = e2e_measure(e2e_step_calls, e2e_steps)
+    e2e_steps = max(3, min(steps, 5))
+    e2e_calls_value = e2e_measure(e2e_calls, e2e_steps)
     calls_bytes = hits_pinned.numpy().tobytes()
     hits_pinned.zero_()
-    e2e_value = e2e_measure(e2e_step, e2e_steps)
+    e2e_value = e2e_measure(e2e_host, e2e_steps)
     e2e_same = hits_pinned.numpy().tobytes() == calls_bytes
-    host_launches = tr.dev.stats()["kernel_launches"]
-    hits = np.frombuffer(hits_pinned.numpy().tobytes(), dtype=tracer_mod.HIT_DT)
+    host_launches = dev.stats()["kernel_launches"]
+    hits = np.frombuffer(calls_bytes, dtype=tracer_mod.HIT_DT)
     hit_frac = float((hits["dist"] < 1e30).mean())
 
+    dev.enable_stats(True)
     tr.set_mode(0, 1)                      # strict order = the reference's visiting order => its algorithmic work
-    tr.dev.enable_stats(True)
-    tr.dev.trace_rays(tr.args, rb, R, hb)
-    tr.dev.ready_wait()
-    work = tr.dev.stats()
+    dev.trace_rays(tr.args, rb, R, hb)
+    dev.ready_wait()
+    work_ref = dev.stats()
     tr.set_mode(0, 0)
-    tr.dev.trace_rays(tr.args, rb, R, hb)
-    tr.dev.ready_wait()
-    unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(work, "strict")]
-    tr.dev.enable_stats(False)
-    abytes = 32 * work["box_tests"] + 40 * work["tri_tests"] + 160 * work["blas_entered"] + 48 * R    # + ray in (24 B) and hit record out (24 B)
-    aflops = 27 * work["box_tests"] + 53 * work["tri_tests"] + 30 * work["blas_entered"]
-    k_ms = float(np.mean(kernel_ms))
-    hbm, hbm_src, sm_mhz = peaks()
-    achieved = abytes / (k_ms * 1e-3) / 1e9
-    fp32_peak = tr.dev.caps(0x3) * 128 * 2 * sm_mhz * 1e6 / 1e12
-    traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(name)
-    except Exception:
-        pass
+    dev.trace_rays(tr.args, rb, R, hb)
+    dev.ready_wait()
+    work_own = dev.stats()
+    dev.enable_stats(False)
+    unit_perf = [rt_unit_perf(work_own, "fast"), rt_unit_perf(work_ref, "strict")]
+    abytes = 32 * work_ref["box_tests"] + 40 * work_ref["tri_tests"] + 160 * work_ref["blas_entered"] + 48 * R    # + ray in (24 B) and hit record out (24 B)
+    aflops = 27 * work_ref["box_tests"] + 53 * work_ref["tri_tests"] + 30 * work_ref["blas_entered"]
+    roof = roofline_block(name, "k_render_m<trace> (ray state machine, rays as work items)", k_ms, gpus, work_ref, work_own, abytes, aflops,
+                          own_work(work_own, 0, 48 * R), dev.caps(0x3))
 
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        po = importlib.import_module("oracle.pyoracle")
-        orc, kind = cpu_oracle()
-        raw = po.RawScene(orc, bufs, karg)       # the oracle's hot loop on the very bytes that were uploaded
-        sample = rays[: 1 << 18]
-        threads = orc.hw_threads()
-        best = None
-        for _ in range(2):
-            t0 = time.perf_counter()
-            ref_hits = raw.trace_rays(sample, threads=threads)
-            dt = time.perf_counter() - t0
-            best = dt if best is None or dt < best else best
-        same = (ref_hits["triIdx"] == hits["triIdx"][: len(sample)]) & (ref_hits["dist"] == hits["dist"][: len(sample)])
-        cpu = {"value": len(sample) / best / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
-               "sample": f"first {len(sample)} rays of rank 0's shard, all host threads, best of 2",
-               "gpu_hit_records_identical_on_sample": float(same.mean())}
-    if rank == 0:
-        ntri = 2 * wl["n"] ** 2
-        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic",
-                "config": {"workload": name, "baseline_config_index": wl["config_index"], "triangles": ntri, "scene_scale": wl.get("scale", 1.0), "rays_per_gpu": R,
-                           "rays_per_step": rays_step, "hit_fraction": hit_frac,
-                           "partition": f"rays sharded by index over {world} GPU(s), scene replicated, no collective on the data path",
-                           "l2": "512 MB memset between timed iterations (L2 flush); working set (scene 1.6 GB at 10 M triangles) >> L2",
-                           "host_bvh_build_s": round(build_s, 3)},
-                "clocks": clocks,
-                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 24, "steps": e2e_steps,
-                        "timer": "host wall clock around vx_b200_trace_rays_host (pinned host rays in, pinned host hit records out; "
-                                 "chunks pipelined on three streams), max over ranks",
-                        "launches_per_step": int(host_launches),
-                        "four_call_sequence": {"value": e2e_calls_value, "unit": "Mrays/s", "identical_records": bool(e2e_same),
-                                               "calls": "vx_copy_to_dev(rays) + vx_b200_trace_rays + vx_ready_wait + vx_copy_from_dev(hits)"}},
-                "gpu_launches": int(launches_per_step) * args.steps, "rt_unit_perf": unit_perf,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": traffic,
-                             "peak_source": hbm_src, "kernel": "k_render_m<trace> (ray state machine, rays as work items)", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": abytes,
-                             "algorithmic_bytes_per_ray": abytes / R,
-                             "fp32": {"achieved_tflops": aflops / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
-                                      "frac": aflops / (k_ms * 1e-3) / 1e12 / fp32_peak},
-                             "work_per_ray": {k: work[k] / R for k in ("box_tests", "tri_tests", "blas_entered")},
-                             "l2_gather": gather_roofline(tr.dev, achieved, beyond_l2=ntri >= 4_000_000)},
-                "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+    # parity + CPU baseline: the checker's hot loop on the very bytes that were uploaded, first 2^18 rays of the set
+    po = importlib.import_module("oracle.pyoracle")
+    par = pkg("parity")
+    orc, kind = cpu_oracle()
+    raw = po.RawScene(orc, bufs, karg)
+    sample = rays[: 1 << 18]
+    threads = orc.hw_threads()
+    best = None
+    for _ in range(2 if cpu else 1):
+        t0 = time.perf_counter()
+        ref_hits = raw.trace_rays(sample, threads=threads)
+        dt = time.perf_counter() - t0
+        best = dt if best is None or dt < best else best
+    hp = par.hit_parity(hits[: len(sample)], ref_hits)
+    parity = {"checker": kind, "checked_order": "fast (the timed configuration)", "rays": hp["n"], "id_mismatch": hp["mismatch"], "ties": hp["ties"],
+              "non_tie": hp["non_tie"], "max_rel_t": hp["max_rel_t"], "bit_exact_t": hp["bit_exact_t"],
+              "green": bool(hp["non_tie"] == 0 and hp["mismatch_frac"] <= 1e-4 and hp["max_rel_t"] <= 1e-5),
+              "host_entry_point_records_identical": bool(e2e_same)}
+    cpu_b = {"value": len(sample) / best / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
+             "sample": f"first {len(sample)} rays of the set, all host threads, best of {2 if cpu else 1}"}
+    rb.free()
+    hb.free()
     tr.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    ntri = 2 * wl["n"] ** 2
+    return {"workload": name, "baseline_config_index": wl["config_index"], "value": value, "unit": "Mrays/s", "n_gpus": gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": total_ms / steps, "rays_per_step": R, "triangles": ntri, "scene_scale": wl.get("scale", 1.0),
+            "hit_fraction": hit_frac, "per_gpu_kernel_ms": {"slowest": k_ms, "fastest": float(np.mean([r[2] for r in runs]))},
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 24, "steps": e2e_steps,
+                    "timer": "host wall clock around vx_b200_trace_rays_host (pinned host rays in, pinned host hit records out; chunks "
+                             "pipelined on three streams per GPU)", "launches_per_step": int(host_launches),
+                    "four_call_sequence": {"value": e2e_calls_value, "unit": "Mrays/s",
+                                           "calls": "vx_copy_to_dev(rays) + vx_b200_trace_rays + vx_ready_wait + vx_copy_from_dev(hits)"}},
+            "gpu_launches": launches * steps, "rt_unit_perf": unit_perf, "roofline": roof, "parity": parity, "cpu_baseline": cpu_b, "clocks": clk,
+            "host_bvh_build_s": round(build_s, 3)}
 
 
-def quick_run(name, local, steps=5, kernel=0):
-    """kernel-only Mrays/s of another workload on one GPU (reported under config.extra_workloads; not the headline)."""
-    tracer_mod, host = pkg("tracer"), pkg("host")
-    wl = WORKLOADS[name]
-    hs = host.HostScene(make_meshes(wl))
-    karg = hs.setup(wl["w"], wl["h"], spp=1, max_depth=wl["depth"])
-    tr = tracer_mod.Tracer(wl["w"], wl["h"], 1, wl["depth"], cuda_device=local).init(hs.buffers())
-    tr.setup({k: karg[k][0] for k in karg.dtype.names})
-    tr.set_mode(wl["mode"], 0, kernel=kernel)
-    tr._upload_args()
-    ms = []
-    for i in range(steps + 3):
-        tr.launch()
-        if i >= 3:
-            ms.append(tr.dev.last_kernel_ms())
-    rays = tr.dev.stats()["rays"]
-    tr.close()
-    return {"mrays_per_s": rays / (float(np.mean(ms)) * 1e3), "kernel_ms": float(np.mean(ms)), "rays_per_step": rays,
-            "note": "kernel time only, L2 not flushed (working set > L2 for the 1M-triangle scenes' framebuffer+scene)"}
-
-
-def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
+def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
     """layout B (simx RT-unit path, quantized BVH4): kernel-only Mrays/s of k_rtu_render on the cfg1 geometry, its algorithmic
     bytes (52 B per node read + 52 B per instance entered + 36 B per triangle tested + 156 B per shaded hit + 4 B per
     pixel, counted in the reference's own visiting order) and the CPU-RTU baseline (the reference's rt_traversal.cpp when
@@ -692,13 +627,14 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
     karg = hs.setup(w, h, spp=1, max_depth=1)
     bufs = hs.buffers()
     build_s = time.perf_counter() - t0
-    tr = rtx.RtxTracer(w, h, 1, 1, cuda_device=local).init(bufs)
+    tr = rtx.RtxTracer(w, h, 1, 1, cuda_device=0).init(bufs)
     tr.setup({k: karg[k][0] for k in karg.dtype.names}, camera=rtx.CAMERA_PINHOLE)
     tr._upload_args()
     ms = []
-    for i in range(steps + 3):
+    for i in range(steps + 4):
+        tr.dev.flush_l2()
         tr.launch()
-        if i >= 3:
+        if i >= 4:
             ms.append(tr.dev.last_kernel_ms())
     rays = tr.dev.stats()["rays"]
     tr.set_order(1)
@@ -714,6 +650,7 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
     tr.set_program(0)
     pms = []
     for i in range(steps + 2):
+        tr.dev.flush_l2()
         tr.launch()
         if i >= 2:
             pms.append(tr.dev.last_kernel_ms())
@@ -722,16 +659,16 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
     tr.close()
     abytes = 52 * wk["box_tests"] + 52 * wk["blas_entered"] + 36 * wk["tri_tests"] + 156 * wk["shaded_hits"] + 4 * w * h
     k_ms = float(np.mean(ms))
-    hbm, _, _ = peaks()
-    out = {"mrays_per_s": rays / (k_ms * 1e3), "kernel": "k_rtu_render (fast order)", "kernel_ms": k_ms, "rays_per_step": rays,
+    m = ncu_metrics("rtu_1080p_primary_100k")
+    out = {"mrays_per_s": rays / (k_ms * 1e3), "kernel": "k_rtu_render (fast order)", "kernel_ms": k_ms, "steps": steps, "rays_per_step": rays,
            "strict_order_kernel_ms": strict_ms, "host_bvh4_build_s": round(build_s, 3),
-           "algorithmic_bytes_per_ray": abytes / max(1, rays), "roofline_hbm_frac": abytes / (k_ms * 1e-3) / 1e9 / hbm,
+           "algorithmic_bytes_per_ray": abytes / max(1, rays), "algorithmic_gbs_reference_order": abytes / (k_ms * 1e-3) / 1e9,
            "work_per_ray": {"nodes": wk["box_tests"] / max(1, rays), "tri_tests": wk["tri_tests"] / max(1, rays),
                             "blas_entered": wk["blas_entered"] / max(1, rays), "shaded_hits": wk["shaded_hits"] / max(1, rays)},
-           "rt_unit_perf": unit_perf,
+           "rt_unit_perf": unit_perf, "ncu": m,
            "shader_program_kernel": {"kernel": "k_rtu_program<ShippedShaders> (fast order)", "kernel_ms": program_ms,
                                      "mrays_per_s": rays / (program_ms * 1e3)},
-           "note": "kernel time only, L2 not flushed; algorithmic work = the reference's trail/short-stack order (strict)"}
+           "note": "kernel time only (CUDA events), L2 flushed before every frame; algorithmic work = the reference's trail/short-stack order (strict)"}
     if with_cpu:
         R = importlib.import_module("oracle.pyoracle_rtu")
         orc = R.best()
@@ -751,6 +688,78 @@ def quick_run_rtu(local, n=224, w=1920, h=1080, steps=5, with_cpu=True):
     return out
 
 
+def run_b200(args, name):
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    gloo = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        one = torch.ones(1, device=f"cuda:{local}")
+        dist.all_reduce(one)                       # the rendezvous the launcher expects: N ranks, one per GPU
+        torch.cuda.synchronize()
+        assert int(one.item()) == world
+        gloo = dist.new_group(backend="gloo")      # the long wait below happens on the CPU, not in a spinning NCCL kernel
+        if rank != 0:
+            del one
+            torch.cuda.empty_cache()
+            dist.barrier(group=gloo)               # rank 0 drives all N GPUs through ONE vx device (the backend's multi-GPU path)
+            dist.destroy_process_group()
+            return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: the b200 backend has no CPU fallback")
+    if torch.cuda.device_count() < args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but {torch.cuda.device_count()} visible")
+    if args.fb:
+        os.environ["VORTEX_B200_FB"] = args.fb
+    if args.collective:
+        os.environ["VORTEX_B200_COLLECTIVE"] = args.collective
+    wl = WORKLOADS[name]
+    incoherent = "rays_per_gpu" in wl
+    head = (measure_incoherent(name, args.gpus, args.steps, args.warmup, cpu=not args.no_cpu, clocks=True) if incoherent else
+            measure_frames(name, args.gpus, args.steps, args.warmup, kernel=args.kernel, cpu=not args.no_cpu, clocks=True))
+    secondary = {}
+    if args.extra:
+        sec_steps = max(20, args.steps)
+        for other in SECONDARY:
+            if other != name:
+                secondary[other] = measure_frames(other, args.gpus, sec_steps, args.warmup, kernel=args.kernel)
+        if args.gpus >= 8 and not incoherent:
+            secondary["cfg4_incoherent_10m"] = measure_incoherent("cfg4_incoherent_10m", args.gpus, sec_steps, args.warmup)
+        secondary["rtu_1080p_primary_100k"] = quick_run_rtu(steps=sec_steps, with_cpu=not args.no_cpu)
+    multi = ("one vx_device_h over %d GPUs in one process (vx_b200_select_gpus): uploads sliced over %d PCIe links and replicated over "
+             "NVLink (%s), %d-row bands round-robin, band-wise download (%s)" %
+             (args.gpus, args.gpus, "ncclAllGather" if args.collective == "nccl" else "peer copies", BAND_ROWS,
+              "kernels store into GPU 0's framebuffer over NVLink" if args.fb == "peer" else "each GPU copies its own bands to the host")
+             ) if args.gpus > 1 else "single GPU"
+    cfg = {"workload": name, "baseline_config_index": wl["config_index"], "triangles": head["triangles"], "rays_per_step": head["rays_per_step"],
+           "multi_gpu": multi, "torchrun_world": world,
+           "l2": "512 MB memset on every GPU before each timed step (vx_b200_flush_l2), outside the timed pair of events",
+           "timing": "CUDA events on GPU 0's stream: begin event (all GPUs' streams wait for it) .. end event after joining every GPU's end "
+                     "event (vx_b200_stats_t.group_ms)",
+           "schedule_feedback": "on (DESIGN 5): tile groups handed out in descending order of the cost recorded on earlier frames when a "
+                                "timed trial during warm-up found that faster; `schedule_feedback_off` carries the row-major figure",
+           "host_bvh_build_s": head["host_bvh_build_s"], "secondary_workloads": secondary}
+    for k in ("width", "height", "mode", "max_depth", "scene_scale", "hit_fraction"):
+        if k in head:
+            cfg[k] = head[k]
+    line = {"metric": METRIC, "value": head["value"], "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": head["warmup"],
+            "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak" if incoherent else "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": cfg, "clocks": head["clocks"], "e2e": head["e2e"], "gpu_launches": head["gpu_launches"],
+            "parity": head["parity"], "roofline": head["roofline"], "cpu_baseline": head["cpu_baseline"], "rt_unit_perf": head["rt_unit_perf"],
+            "per_gpu_kernel_ms": head["per_gpu_kernel_ms"]}
+    if "schedule_feedback_off" in head:
+        line["schedule_feedback_off"] = head["schedule_feedback_off"]
+    print(json.dumps(line), flush=True)
+    if gloo is not None:
+        import torch.distributed as dist
+        dist.barrier(group=gloo)
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -758,22 +767,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
-    ap.add_argument("--scene-upload", default="auto", choices=["auto", "broadcast", "replicate"],
-                    help="N > 1, end-to-end leg: rank 0 uploads + NCCL broadcast, or every rank uploads; auto = broadcast from 4 GPUs up "
-                         "(measured: 2 GPUs 4915 vs 5152, 4 GPUs 5757 vs 5399, 8 GPUs 6136 vs 4058 Mrays/s)")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (the parity checker still runs)")
     ap.add_argument("--kernel", type=int, default=0, help="layout-A render kernel: 0 = ray state machine (default), 1 = one pixel per lane")
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: how the bands reach rank 0's framebuffer")
-    ap.add_argument("--extra", type=int, default=1, help="also report kernel-only numbers of the 1M-triangle workloads (N=1)")
+    ap.add_argument("--fb", default=None, choices=["local", "peer"], help="N > 1: each GPU keeps its bands (default) / kernels store into GPU 0's framebuffer")
+    ap.add_argument("--collective", default=None, choices=["peer", "nccl"], help="N > 1: scene replication by peer copies (default) / ncclAllGather")
+    ap.add_argument("--extra", type=int, default=1, help="also measure the secondary workloads (config.secondary_workloads)")
     args = ap.parse_args()
-    name = args.workload or ("cfg1_1080p_primary+shadow_100k" if args.gpus == 1 else "cfg3_8k_primary+shadow_1m")
-    wl = WORKLOADS[name]
+    name = args.workload or DEFAULT_WORKLOAD
     if args.impl == "reference":
-        run_reference(args, wl, name)
-    elif "rays_per_gpu" in wl:
-        run_incoherent(args, wl, name)
+        run_reference(args, WORKLOADS[name], name)
     else:
-        run_b200(args, wl, name)
+        run_b200(args, name)
 
 
 if __name__ == "__main__":

@@ -139,6 +139,28 @@ int vx_dump_perf(vx_device_h hdevice, FILE *stream);                            
 /* Which CUDA device the NEXT vx_dev_open() binds (default: env VORTEX_B200_DEVICE, else LOCAL_RANK, else 0). */
 int vx_b200_select_device(int cuda_device);
 
+/* How many GPUs of this box the NEXT vx_dev_open() spans (default: env VORTEX_B200_GPUS, else 1).  The vx_* API stays
+ * single-device (the reference host opens ONE handle and reads ONE framebuffer: runtime/stub/vortex.cpp:53-97,
+ * tests/regression/raycast/tracer.cpp:231-240) — with N > 1 the backend
+ *   - keeps one arena per GPU with identical Vortex addresses;
+ *   - vx_copy_to_dev: large buffers enter the box ONCE, slice i/N through GPU i's own PCIe link, and are replicated to the other
+ *     GPUs over NVLink (peer copies that follow the slices; VORTEX_B200_COLLECTIVE=nccl: one ncclAllGather instead);
+ *   - vx_start: 8-row bands of the image round-robin over the GPUs, one persistent kernel per GPU on its own stream;
+ *   - vx_copy_from_dev(framebuffer): every GPU copies its own bands straight into the caller's buffer (one strided copy per
+ *     GPU over its own PCIe link); any other read of the framebuffer first gathers the bands on GPU 0 over NVLink;
+ *   - vx_b200_trace_rays / _host: rays sharded by index.
+ * Devices used: first .. first+N-1 (first = vx_b200_select_device / VORTEX_B200_DEVICE, default 0 when N > 1). */
+int vx_b200_select_gpus(int n_gpus);
+
+/* Asynchronous readback (N >= 1): after this call every vx_start whose framebuffer is `hframebuffer` is followed, on the GPU
+ * streams, by the copy of the finished image into `host_ptr` (page-locked memory of at least width*height*4 bytes; each GPU
+ * copies its own bands), so that vx_ready_wait returns with the image already in host memory and the vx_copy_from_dev of the
+ * whole framebuffer into that same pointer has nothing left to do.  host_ptr == NULL cancels. */
+int vx_b200_set_readback(vx_device_h hdevice, vx_buffer_h hframebuffer, void *host_ptr, uint64_t bytes);
+
+/* Write 512 MB of scratch on every GPU of the device (stream-ordered): flushes the 126 MB L2 between timed iterations. */
+int vx_b200_flush_l2(vx_device_h hdevice);
+
 /* Screen-space partition for multi-GPU runs: the image is cut into bands of `band_rows` rows and this
  * device renders band j iff j % world == rank.  Pixels of other bands are left untouched.
  * world == 1 (default) renders everything.  Env defaults: VORTEX_B200_RANK / VORTEX_B200_WORLD. */
@@ -187,6 +209,21 @@ typedef struct {
   uint64_t lane_steps;      /* traversal iterations summed over lanes   (~ rt_total_thread_latency) */
   uint64_t warp_steps;      /* traversal iterations issued by warps      (~ rt_total_warp_latency) */
   uint64_t warps;           /* warps that ran                            (~ rt_total_warps) */
+  /* one vx_device_h over several GPUs (VORTEX_B200_GPUS / vx_b200_select_gpus): the counters above are sums over the GPUs,
+   * kernel_ms / prep_ms the maxima; group_ms is the device time from the moment every GPU may start to the moment the last
+   * one (and any readback copy) finished, taken by CUDA events on GPU 0's stream which joins the others */
+  uint32_t gpus;
+  float group_ms;
+  float kernel_ms_min, kernel_ms_max;   /* fastest / slowest GPU of the run */
+  /* RT-unit latency distribution (statistics mode; the shape of RTUnit::PerfStats::rt_latency_dist[warp_statuses][ray_statuses],
+   * sim/simx/rt_unit.h:24, in lane-iterations of the ray state machine instead of simulated cycles).  Row = what the warp was
+   * doing: 0 fetching work (GEN), 1 shading (POST), 2 traversing (TRAV).  Column = what a lane of that warp was doing meanwhile:
+   * 0 awaiting_processing (traversal finished, waiting for POST), 1 awaiting_scheduling (empty slot, waiting for GEN),
+   * 2 awaiting_mf (holds a node of the other kind than the one the warp is stepping), 3 executing_op (takes part in the step),
+   * 4 trace_complete (retired: no work left for this lane). */
+  uint64_t latency_dist[3][5];
+  /* traversal steps per ray, log2 buckets: [0] = 0 steps, [k] = 2^(k-1) .. 2^k - 1 steps, [15] = 2^14 and more */
+  uint64_t steps_hist[16];
 } vx_b200_stats_t;
 
 /* Statistics of the last completed run.  Work counters other than `rays` are gathered only after

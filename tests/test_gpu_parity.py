@@ -339,3 +339,98 @@ def test_gpu_gather_probe_reports_a_bandwidth():
             dev.probe_gather(32 << 20, 48)
     finally:
         dev.close()
+
+
+def test_partial_upload_into_large_instance_buffer(oracle):
+    """a host that patches ONE blas_node_t of a > 4 KB instance buffer (27 instances x 160 B) with a small vx_copy_to_dev: the
+    backend's host copy of small uploads must not be mistaken for the whole buffer (instance bases of the 4-wide records)"""
+    # 27 instances of ONE mesh placed by their transforms, as the reference app does with -n (raycast/tracer.cpp:89-100).  (Meshes
+    # that differ are not usable here: the reference's BVH leaves index triIdx relative to the mesh's own slice while render.h
+    # indexes the global buffer (raycast/scene.cpp:62 vs render.h:88-90), so instance i > 0 shows mesh 0's triangles.)
+    def shift(x, y, z):
+        m = np.eye(4, dtype=np.float32)
+        m[0, 3], m[1, 3], m[2, 3] = x, y, z
+        return m
+    base = scenes.icosphere((0, 0, 0), 0.17, 1)
+    meshes = [dict(base, transform=shift(0.4 * (i % 3 - 1), 0.4 * ((i // 3) % 3 - 1), 0.4 * (i // 9 - 1))) for i in range(27)]
+    sc = oracle.scene_create(meshes)
+    karg = sc.setup(320, 240)
+    ref, _ = sc.render(mode=0, threads=oracle.hw_threads())
+    tr = tracer_for(sc, karg)
+    try:
+        blas = tr.host_scene["blas"]
+        assert blas.nbytes == 27 * 160 > 4096
+        for strict in (1, 0):
+            tr.set_mode(0, strict)
+            assert channel_diff(tr.run(), ref) <= (0 if strict else 1)
+            for k in (5, 26):
+                tr.bufs["blas"].copy_to_dev(np.ascontiguousarray(blas[k * 160:(k + 1) * 160]), dst_offset=k * 160)
+                assert channel_diff(tr.run(), ref) <= (0 if strict else 1), (strict, k)
+        # moving one instance through a small upload is seen by the next frame
+        moved = blas.copy().view(np.float32).reshape(27, 40)
+        moved[3, 16 + 3] += 0.1                      # invTransform translation x of instance 3 (cells 3 / 7 / 11)
+        tr.bufs["blas"].copy_to_dev(np.ascontiguousarray(moved[3]).view(np.uint8), dst_offset=3 * 160)
+        img = tr.run()
+        assert (img != ref).any()
+        rs = po.RawScene(oracle, dict(tr.host_scene, blas=moved.view(np.uint8).reshape(-1)), karg)
+        ref2, _ = rs.render(mode=0, threads=oracle.hw_threads())
+        assert channel_diff(img, ref2) <= 1
+    finally:
+        tr.close()
+
+
+def test_argument_buffer_with_headroom_is_a_raycast_launch(oracle):
+    """a raycast host whose kernel_arg_t sits in a larger buffer (256 bytes, or at an offset) is still layout A: the layout is
+    taken from the RT-unit DCRs / VX_DCR_B200_RT_LAYOUT, the size is only a lower bound"""
+    sc = oracle.scene_create([scenes.cornell_box()])
+    karg = sc.setup(96, 64)
+    tr = tracer_for(sc, karg)
+    try:
+        tr.set_mode(0, 1)
+        want = tr.run().copy()
+        big = tr.dev.mem_alloc(256)
+        big.copy_to_dev(np.frombuffer(tr.karg.tobytes() + b"\0" * 64, dtype=np.uint8))
+        tr.out.copy_to_dev(np.zeros((64, 96), np.uint32))
+        tr.dev.start(tr.krnl, big)
+        tr.dev.ready_wait()
+        got = np.zeros((64, 96), np.uint32)
+        tr.out.copy_from_dev(got)
+        assert np.array_equal(got, want)
+        big.free()
+    finally:
+        tr.close()
+
+
+def test_deep_tree_overflow_is_reported_not_silent():
+    """a degenerate BVH2 deeper than the reference's own stack[64] (render.h:80): every push is bounds-checked, the run is
+    reported as failed (error bit 0) instead of writing past the traversal stack"""
+    n = 200                                           # a chain: every inner node = (next inner node, one leaf); all boxes equal
+    tris = np.zeros((n, 9), np.float32)
+    tris[:, 0:3] = (-1, -1, 0)
+    tris[:, 3:6] = (1, -1, 0)
+    tris[:, 6:9] = (0, 1, 0)
+    tris[:, 2::3] += (np.arange(n, dtype=np.float32) * 0.01)[:, None]
+    nodes = np.zeros(2 * n, dtype=[("mn", "<f4", 3), ("leftFirst", "<u4"), ("mx", "<f4", 3), ("triCount", "<u4")])
+    nodes["mn"], nodes["mx"] = (-1, -1, -1), (1, 1, 3)
+    # inner k (root = node 0, else node 2k-1) has children 2k+1 (the next inner node; equal distances => visited first in strict
+    # order) and 2k+2 (leaf k, pushed): one stack entry per level
+    for k in range(n - 1):
+        inner = 0 if k == 0 else 2 * k - 1
+        nodes[inner]["leftFirst"], nodes[inner]["triCount"] = 2 * k + 1, 0
+        nodes[2 * k + 2]["leftFirst"], nodes[2 * k + 2]["triCount"] = k, 1
+    nodes[2 * n - 3]["leftFirst"], nodes[2 * n - 3]["triCount"] = n - 1, 1
+    port = po.PortRaycast() if po.have_port() else best_oracle()
+    sc = port.scene_create([{"tris": tris, "triex": np.zeros((n, 15), np.float32), "tex": np.full((2, 2), 0x808080, np.uint32)}])
+    karg = sc.setup(32, 32)
+    bufs = dict(sc.buffers())
+    bufs["bvh"] = nodes.view(np.uint8).reshape(-1).copy()
+    bufs["triIdx"] = np.arange(n, dtype=np.uint32).view(np.uint8)
+    tr = tracer_mod.Tracer(32, 32, 1, 1).init(bufs)
+    try:
+        tr.setup({k: karg[k][0] for k in karg.dtype.names})
+        for kernel in (0, 1):
+            tr.set_mode(0, 1, kernel=kernel)          # strict order pushes one entry per level: depth 200 > 128 / 64
+            with pytest.raises(vx.VxError, match="stack overflow"):
+                tr.run()
+    finally:
+        tr.close()

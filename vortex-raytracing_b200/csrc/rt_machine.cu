@@ -26,6 +26,10 @@ constexpr uint32_t kKindShift = 27;          // bits 27..30: 0 = inner node pair
 constexpr uint32_t kPay = (1u << kKindShift) - 1;
 constexpr uint32_t kReadNode = 15u;
 
+// One array serves both levels; the reference keeps 64 entries per level (render.h:80,151), so 128 here never overflows on a
+// tree the reference can walk.  Every push is bounds-checked: overflow sets error bit 0 and vx_ready_wait fails the run.
+constexpr uint32_t kMachineStack = 2 * kStackSize;
+
 constexpr uint32_t S_EMPTY = 0, S_TRAV = 1, S_DONE = 2, S_MASK = 3;
 constexpr uint32_t F_ANY = 4, F_NAN = 8, F_INBLAS = 16, F_OCCL = 32;
 
@@ -56,6 +60,7 @@ struct Lane {
   uint32_t hblas, htri;
   uint32_t cur, sp, st;
   uint32_t blas;
+  uint32_t steps;         // statistics builds: traversal steps of the ray in this slot
   const uint8_t *nodes;   // first node of the instance being traversed
   const uint8_t *wide;    // its 4-wide records (fast order), same node indexing
 };
@@ -92,7 +97,19 @@ __device__ __forceinline__ void start_ray(Lane &L, const Smem &sm, const SceneA 
   L.dist = tmax, L.bx = 0.f, L.by = 0.f, L.hblas = 0, L.htri = 0;
   L.cur = kTlasTag | sc.tlas_root;
   L.sp = 0;
+  L.steps = 0;
   lc.rays++;
+}
+
+// statistics builds: one lane-iteration of the latency table (WorkCounters::latency): row = what the warp is doing (0 GEN,
+// 1 POST, 2 TRAV), column = what this lane is doing meanwhile.  Called with the warp converged.
+template <bool STATS>
+__device__ __forceinline__ void lat_note(uint32_t *lat, uint32_t row, uint32_t st, bool active, bool exhausted) {
+  if (STATS) {
+    const uint32_t s = st & S_MASK;
+    const uint32_t col = active ? 3u : (s == S_TRAV ? 2u : (s == S_DONE ? 0u : (exhausted ? 4u : 1u)));
+    lat[row * 5u + col]++;
+  }
 }
 
 template <bool STRICT>
@@ -123,9 +140,13 @@ __device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool caref
   uint32_t eR = enc_child(__float_as_uint(r0.w), __float_as_uint(r1.w), first + 1);
   if (hitL && hitR) {
     bool right_next = STRICT ? (dL < dR) : (dR < dL);   // STRICT: the reference visits the FARTHER child first (render.h:113-118)
-    stk_e[L.sp] = right_next ? eL : eR;
-    if (!STRICT) stk_d[L.sp] = right_next ? dL : dR;
-    ++L.sp;
+    if (L.sp < kMachineStack) {
+      stk_e[L.sp] = right_next ? eL : eR;
+      if (!STRICT) stk_d[L.sp] = right_next ? dL : dR;
+      ++L.sp;
+    } else {
+      lc.err |= 1u;
+    }
     L.cur = right_next ? eR : eL;
   } else if (hitL) {
     L.cur = eL;
@@ -177,7 +198,7 @@ __device__ __forceinline__ void step_wide(Lane &L, bool careful, uint32_t *stk_e
   VXB_CSWAP(0, 1) VXB_CSWAP(2, 3) VXB_CSWAP(0, 2) VXB_CSWAP(1, 3) VXB_CSWAP(1, 2)
 #undef VXB_CSWAP
   if (d[0] < kInf) {
-    if (L.sp + 3 <= kStackSize) {
+    if (L.sp + 3 <= kMachineStack) {
       if (d[3] < kInf) { stk_e[L.sp] = e[3]; stk_d[L.sp] = d[3]; ++L.sp; }
       if (d[2] < kInf) { stk_e[L.sp] = e[2]; stk_d[L.sp] = d[2]; ++L.sp; }
       if (d[1] < kInf) { stk_e[L.sp] = e[1]; stk_d[L.sp] = d[1]; ++L.sp; }
@@ -230,9 +251,13 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       if (STATS) lc.box += 2;
       if (hitL && hitR) {   // near child first at this level (render.h:175-180)
         bool swap = dL > dR;
-        stk_e[L.sp] = kTlasTag | (swap ? left : right);
-        if (!STRICT) stk_d[L.sp] = swap ? dL : dR;
-        ++L.sp;
+        if (L.sp < kMachineStack) {
+          stk_e[L.sp] = kTlasTag | (swap ? left : right);
+          if (!STRICT) stk_d[L.sp] = swap ? dL : dR;
+          ++L.sp;
+        } else {
+          lc.err |= 1u;
+        }
         L.cur = kTlasTag | (swap ? right : left);
       } else if (hitL) {
         L.cur = kTlasTag | left;
@@ -290,7 +315,7 @@ __device__ __forceinline__ bool is_inner(const Lane &L) { return (L.st & S_MASK)
 // TRAV: runs until fewer than `quorum` lanes of the warp are still traversing
 template <bool STRICT, bool STATS, bool COST>
 __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &sc, uint32_t quorum, uint32_t inner_quorum, uint32_t *stk_e,
-                                         float *stk_d, Local &lc) {
+                                         float *stk_d, Local &lc, uint32_t *lat, bool exhausted) {
   for (;;) {
     // warp-uniform choice of the NaN-exact min/max path (no divergence); F_NAN only changes in step_other / start_ray
     const bool careful = __any_sync(0xffffffffu, (L.st & (S_MASK | F_NAN)) == (S_TRAV | F_NAN));
@@ -298,15 +323,19 @@ __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &
       bool inner = is_inner(L);
       unsigned m = __ballot_sync(0xffffffffu, inner);
       if ((uint32_t)__popc(m) < inner_quorum) break;
+      lat_note<STATS>(lat, 2, L.st, inner, exhausted);
       if (inner) {
         simt_step<STATS>(lc);
+        if (STATS) L.steps++;
         if (COST) sm.u(C_T0) += 1u;
         if (STRICT) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);   // the reference's own BVH2 walk
         else step_wide<STATS>(L, careful, stk_e, stk_d, lc);                        // 4-wide records (the launch guarantees sc.wide)
       }
     }
+    lat_note<STATS>(lat, 2, L.st, (L.st & S_MASK) == S_TRAV && !is_inner(L), exhausted);
     if ((L.st & S_MASK) == S_TRAV && !is_inner(L)) {
       simt_step<STATS>(lc);
+      if (STATS) L.steps++;
       if (COST) sm.u(C_T0) += 1u;
       step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
     }
@@ -466,8 +495,8 @@ template <uint32_t MODE, bool STRICT, bool STATS, bool COST>
 __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(const __grid_constant__ RenderA p) {
   constexpr uint32_t kCols = (MODE == kModeTrace) ? C_BASE_END : ((MODE & 1u) ? C_SHADOW_END : C_BASE_END);
   __shared__ float s_cols[kCols * kBlockThreads];
-  uint32_t stk_e[kStackSize];
-  float stk_d[kStackSize];
+  uint32_t stk_e[kMachineStack];
+  float stk_d[kMachineStack];
   const Smem sm{s_cols, threadIdx.x};
   const KernelArgA &a = p.arg;
   const uint32_t lane = threadIdx.x & 31;
@@ -484,7 +513,11 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   Lane L;
   L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.wide = reinterpret_cast<const uint8_t *>(p.scene.wide), L.blas = 0;
   L.o = L.d = L.id = mk3(0, 0, 0);
+  L.steps = 0;
   Local lc{0, 0, 0, 0, 0};
+  uint32_t lat[STATS ? 15 : 1];
+  if (STATS)
+    for (int k = 0; k < 15; ++k) lat[k] = 0;
   uint32_t chunk_next = 0, chunk_end = 0;
   bool exhausted = (f.total == 0);
 
@@ -493,10 +526,13 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
     unsigned done = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_DONE);
     const uint32_t quorum = exhausted ? 1u : p.quorum_refill;
     if (trav && ((uint32_t)__popc(trav) >= quorum || (!done && exhausted))) {
-      traverse<STRICT, STATS, COST>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk_e, stk_d, lc);
+      traverse<STRICT, STATS, COST>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk_e, stk_d, lc, lat, exhausted);
       continue;
     }
     if (done) {
+      lat_note<STATS>(lat, 1, L.st, (L.st & S_MASK) == S_DONE, exhausted);
+      if (STATS && (L.st & S_MASK) == S_DONE)   // the ray in this slot is complete: its step count goes into the histogram
+        atomicAdd(&p.counters->steps_hist[L.steps ? min(15, 32 - __clz(L.steps)) : 0], 1ull);
       if ((L.st & S_MASK) == S_DONE) post<MODE, STATS, COST>(L, sm, p, lc);
       continue;   // POST may have queued follow-up rays; re-evaluate before pulling new pixels
     }
@@ -546,6 +582,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
         }
         }
       }
+      lat_note<STATS>(lat, 0, L.st, take, false);
       unsigned took = __ballot_sync(0xffffffffu, take);
       chunk_next += (uint32_t)__popc(took);
       need &= ~took;
@@ -553,6 +590,11 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   }
   __syncwarp();
   flush_counters(p.counters, lc, STATS);
+  if (STATS)
+    for (int k = 0; k < 15; ++k) {
+      const unsigned v = __reduce_add_sync(0xffffffffu, lat[k]);
+      if (lane == 0 && v) atomicAdd(&p.counters->latency[k], (unsigned long long)v);
+    }
 }
 
 template <uint32_t MODE, bool STRICT, bool STATS>

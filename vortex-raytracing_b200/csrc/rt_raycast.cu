@@ -75,9 +75,13 @@ __device__ __forceinline__ bool blas_intersect(const SceneA &sc, uint32_t blasId
       if (hitL && hitR) {
         // STRICT: render.h:113-118 pushes the nearer child first, so the FARTHER one is visited first
         bool right_next = STRICT ? (dL < dR) : (dR < dL);
-        stk_e[sp] = right_next ? eL : eR;
-        if (!STRICT) stk_d[sp] = right_next ? dL : dR;
-        ++sp;
+        if (sp < kStackSize) {
+          stk_e[sp] = right_next ? eL : eR;
+          if (!STRICT) stk_d[sp] = right_next ? dL : dR;
+          ++sp;
+        } else {
+          lc.err |= 1u;   // deeper than the reference's own stack[64] (render.h:80): the run is reported as failed
+        }
         cur = right_next ? eR : eL;
         continue;
       } else if (hitL) {
@@ -153,7 +157,8 @@ __device__ __forceinline__ bool tlas_intersect(const SceneA &sc, const Ray &ray,
           uint32_t t = left;
           left = right, right = t;
         }
-        tstack[sp++] = right;
+        if (sp < kStackSize) tstack[sp++] = right;
+        else lc.err |= 1u;
         nodeIdx = left;
         continue;
       } else if (hitL) {

@@ -51,6 +51,9 @@ struct WorkCounters {       // device-resident, zeroed before each run
   unsigned long long rays, box_tests, tri_tests, blas_entered, shaded_hits;
   unsigned long long errors;   // bit 0: a traversal stack overflowed (the run is reported as failed)
   unsigned long long lane_steps, warp_steps, warps;   // statistics mode: SIMT efficiency = lane_steps / (32 * warp_steps)
+  // statistics mode, ray state machine: what the lanes were doing while their warp fetched work / shaded / traversed
+  // (vx_b200_stats_t.latency_dist, the shape of RTUnit::PerfStats::rt_latency_dist) and traversal steps per ray in log2 buckets
+  unsigned long long latency[15], steps_hist[16];
 };
 
 struct RenderA {

@@ -6,6 +6,7 @@
 // ordered copies, vx_start decodes kernel_arg_t and launches the sm_100a ray-tracing kernels, vx_ready_wait
 // is a stream wait.  There is no simulator and no CPU path behind it.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <chrono>
 #include <cstdarg>
@@ -13,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -62,14 +64,7 @@ public:
   Device() : space_(0) {}
   ~Device() { shutdown(); }
 
-  int init() {
-    int count = 0;
-    cudaError_t e = cudaGetDeviceCount(&count);
-    if (e != cudaSuccess || count == 0)
-      return fail("no CUDA device: the b200 backend has no CPU fallback (%s)", e != cudaSuccess ? cudaGetErrorString(e) : "count=0");
-    int dev = g_selected_device;
-    if (dev < 0) dev = (int)env_u64("VORTEX_B200_DEVICE", env_u64("LOCAL_RANK", 0));
-    if (dev >= count) dev = dev % count;
+  int init(int dev) {
     cuda_dev_ = dev;
     CUDA_TRY(cudaSetDevice(cuda_dev_));
     CUDA_TRY(cudaGetDeviceProperties(&prop_, cuda_dev_));
@@ -106,6 +101,11 @@ public:
     if (stream_) cudaStreamSynchronize(stream_);
     if (remote_base_) cudaIpcCloseMemHandle(remote_base_);
     remote_base_ = nullptr, remote_fb_ = nullptr;
+    if (stage_) {
+      cudaFreeHost(stage_);
+      for (auto &e : stage_ev_) if (e) cudaEventDestroy(e), e = nullptr;
+      stage_ = nullptr, stage_next_ = 0;
+    }
     if (gtri_) cudaFree(gtri_);
     if (wide_) cudaFree(wide_);
     if (wide_bases_) cudaFree(wide_bases_);
@@ -198,7 +198,11 @@ public:
     return 0;
   }
 
-  int upload(uint64_t dst, const void *src, uint64_t size) {
+  static constexpr uint64_t kShadowMax = 4096;
+  static constexpr uint64_t kStageMax = 64 << 10;
+  static constexpr int kStageSlots = 32;
+  // defer_sync: the caller (DeviceGroup) waits for the copy itself, after it has issued the other devices' copies
+  int upload(uint64_t dst, const void *src, uint64_t size, bool defer_sync = false) {
     if (size == 0) return 0;
     std::lock_guard<std::mutex> g(mu_);
     if (dst + size > space_.capacity() || dst + size < dst) return fail("upload out of range");
@@ -206,17 +210,43 @@ public:
     uint64_t start = 0;
     if (auto *b = space_.find(dst, size, &start)) {
       b->write_gen = ++generation_;
-      if (size <= 4096) {
-        auto &sh = small_shadow_[start];
-        if (sh.size() < b->size) sh.resize(b->size, 0);
-        if (dst - start + size <= sh.size()) memcpy(sh.data() + (dst - start), src, size);
-      } else {
-        small_shadow_.erase(start);
+      // The host shadow exists only while it is known to hold EVERY byte of the block: it is created by an upload that
+      // covers the whole block (blocks of at most kShadowMax bytes), patched by later partial uploads, and dropped by
+      // anything else that writes the block (a partial upload without a complete shadow, a GPU build, mark_written).
+      auto sh = small_shadow_.find(start);
+      if (dst == start && size == b->size && size <= kShadowMax) {
+        auto &v = small_shadow_[start];
+        v.assign((const uint8_t *)src, (const uint8_t *)src + size);
+      } else if (sh != small_shadow_.end()) {
+        if (sh->second.size() == b->size && dst - start + size <= sh->second.size()) memcpy(sh->second.data() + (dst - start), src, size);
+        else small_shadow_.erase(sh);
       }
     }
+    if (size <= kStageMax) {
+      // small uploads (argument blocks, TLAS / instance records) are copied into a page-locked ring first: the caller's
+      // memory has been read when this returns, the device copy is stream-ordered, and nothing waits for the GPU
+      if (!stage_) {
+        CUDA_TRY(cudaMallocHost(&stage_, kStageMax * kStageSlots));
+        for (auto &e : stage_ev_) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      }
+      const int slot = stage_next_++ % kStageSlots;
+      if (stage_next_ > kStageSlots) CUDA_TRY(cudaEventSynchronize(stage_ev_[slot]));   // the copy that last used this slot
+      memcpy(stage_ + (uint64_t)slot * kStageMax, src, size);
+      CUDA_TRY(cudaMemcpyAsync(arena_ + dst, stage_ + (uint64_t)slot * kStageMax, size, cudaMemcpyHostToDevice, stream_));
+      CUDA_TRY(cudaEventRecord(stage_ev_[slot], stream_));
+      return 0;
+    }
     CUDA_TRY(cudaMemcpyAsync(arena_ + dst, src, size, cudaMemcpyHostToDevice, stream_));
-    CUDA_TRY(cudaStreamSynchronize(stream_));
+    if (!defer_sync) CUDA_TRY(cudaStreamSynchronize(stream_));
     return 0;
+  }
+  // block containing `addr` (DeviceGroup replicates whole blocks)
+  bool block_of(uint64_t addr, uint64_t *start, uint64_t *size) {
+    std::lock_guard<std::mutex> g(mu_);
+    auto *b = space_.find(addr, 1, start);
+    if (!b) return false;
+    *size = b->size;
+    return true;
   }
   int download(void *dst, uint64_t src, uint64_t size) {
     if (size == 0) return 0;
@@ -235,8 +265,7 @@ public:
     CUDA_TRY(cudaSetDevice(cuda_dev_));
     std::vector<uint8_t> args;
     if (fetch_args_locked(args_addr, args) != 0) return -1;
-    uint32_t layout = dcr_get(VX_DCR_B200_RT_LAYOUT);
-    if (layout == 0) layout = (args.size() >= sizeof(KernelArgB)) ? 2 : (args.size() >= sizeof(KernelArgA) ? 1 : 0);
+    uint32_t layout = layout_of_locked(args_addr, args.size());
     if (layout == 1) return start_raycast_locked(args, nullptr, nullptr, 0, 0);
     if (layout == 2) return start_rtu_locked(args);
     return fail("vx_start: argument block of %zu bytes is neither a raycast (192 B) nor a raytracing (216 B) kernel_arg_t", args.size());
@@ -247,9 +276,9 @@ public:
     CUDA_TRY(cudaSetDevice(cuda_dev_));
     std::vector<uint8_t> args;
     if (fetch_args_locked(args_addr, args) != 0) return -1;
-    if (args.size() >= sizeof(KernelArgB) || dcr_get(VX_DCR_B200_RT_LAYOUT) == 2)
-      return trace_rtu_locked(args, rays_addr, count, hits_addr);
-    if (args.size() < sizeof(KernelArgA)) return fail("trace: argument block too small");
+    const uint32_t layout = layout_of_locked(args_addr, args.size());
+    if (layout == 2) return trace_rtu_locked(args, rays_addr, count, hits_addr);
+    if (layout != 1) return fail("trace: argument block too small");
     return start_raycast_locked(args, &hits_addr, rays_addr, count, 1);
   }
 
@@ -264,8 +293,9 @@ public:
     CUDA_TRY(cudaSetDevice(cuda_dev_));
     std::vector<uint8_t> args;
     if (fetch_args_locked(args_addr, args) != 0) return -1;
-    const bool layout_b = args.size() >= sizeof(KernelArgB) || dcr_get(VX_DCR_B200_RT_LAYOUT) == 2;
-    if (!layout_b && args.size() < sizeof(KernelArgA)) return fail("trace: argument block too small");
+    const uint32_t layout = layout_of_locked(args_addr, args.size());
+    const bool layout_b = layout == 2;
+    if (layout == 0) return fail("trace: argument block too small");
     uint64_t chunk = env_u64("VORTEX_B200_HOST_CHUNK", 1ull << 20);   // sweep: profiles/r01_sweep_host_trace.txt
     if (chunk < 4096 || chunk > (1ull << 24)) chunk = 1ull << 20;
     if (chunk > count) chunk = (count + 31) & ~31ull;
@@ -294,6 +324,8 @@ public:
       total.kernel_launches += stats_.kernel_launches, total.prep_launches += stats_.prep_launches;
       total.kernel_ms += stats_.kernel_ms, total.prep_ms += stats_.prep_ms;
       total.lane_steps += stats_.lane_steps, total.warp_steps += stats_.warp_steps, total.warps += stats_.warps;
+      for (int a = 0; a < 15; a++) (&total.latency_dist[0][0])[a] += (&stats_.latency_dist[0][0])[a];
+      for (int a = 0; a < 16; a++) total.steps_hist[a] += stats_.steps_hist[a];
       return 0;
     };
     auto body = [&]() -> int {
@@ -412,8 +444,8 @@ public:
     if (rc != 0) return fail("vx_b200_build_bvh: %s", cudaGetErrorString((cudaError_t)(-rc)));
     // the buffers changed under the caches keyed on upload generations
     uint64_t start = 0;
-    if (auto *b = space_.find(bvh_addr, 1, &start)) b->write_gen = ++generation_;
-    if (auto *b = space_.find(idx_addr, 1, &start)) b->write_gen = ++generation_;
+    if (auto *b = space_.find(bvh_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
+    if (auto *b = space_.find(idx_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
     stats_.kernel_launches = (uint64_t)nl, stats_.prep_launches = 0, stats_.kernel_ms = ms, stats_.prep_ms = 0;
     if (nodes_used) *nodes_used = 2 * tri_count - 1;
     return 0;
@@ -448,10 +480,10 @@ public:
     if (rc != 0) return fail("vx_b200_build_qbvh: %s (capacity %llu nodes, needed %u)", cudaGetErrorString((cudaError_t)(-rc)),
                              (unsigned long long)capacity, used);
     uint64_t start = 0;   // the buffers changed under the caches keyed on upload generations
-    if (auto *b = space_.find(tri_addr, 1, &start)) b->write_gen = ++generation_;
+    if (auto *b = space_.find(tri_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
     if (ex_addr != ~0ull)
-      if (auto *b = space_.find(ex_addr, 1, &start)) b->write_gen = ++generation_;
-    if (auto *b = space_.find(qbvh_addr, 1, &start)) b->write_gen = ++generation_;
+      if (auto *b = space_.find(ex_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
+    if (auto *b = space_.find(qbvh_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
     stats_.kernel_launches = (uint64_t)nl, stats_.prep_launches = 0, stats_.kernel_ms = ms, stats_.prep_ms = 0;
     if (nodes_used) *nodes_used = used;
     return 0;
@@ -497,6 +529,42 @@ public:
     remote_bytes_ = bytes;
     return 0;
   }
+  // ---- hooks for DeviceGroup (one vx_device_h over several GPUs) ----
+  struct Output {            // what the run in flight / the last run wrote
+    uint64_t addr = 0, bytes = 0;
+    uint32_t W = 0, H = 0;   // frames: image size (bands of part_); hit records: W = H = 0
+    bool frame = false, valid = false;
+  };
+  Output last_output() {
+    std::lock_guard<std::mutex> g(mu_);
+    return last_out_;
+  }
+  Partition partition() {
+    std::lock_guard<std::mutex> g(mu_);
+    return part_;
+  }
+  // frames are stored into `owner_arena + dst_addr` (a peer device's arena, same process) instead of this device's arena
+  void set_peer_framebuffer(uint8_t *owner_arena) {
+    std::lock_guard<std::mutex> g(mu_);
+    peer_fb_arena_ = owner_arena;
+  }
+  cudaEvent_t end_event() const { return ev_end_; }
+  bool run_pending() {
+    std::lock_guard<std::mutex> g(mu_);
+    return run_pending_;
+  }
+  // a range of the arena was (or is being, stream-ordered) written by the group: same bookkeeping as an upload
+  int note_written(uint64_t dst, uint64_t size) {
+    std::lock_guard<std::mutex> g(mu_);
+    uint64_t start = 0;
+    if (auto *b = space_.find(dst, size ? size : 1, &start)) {
+      b->write_gen = ++generation_;
+      small_shadow_.erase(start);
+    }
+    return 0;
+  }
+  const cudaDeviceProp &prop() const { return prop_; }
+  uint64_t capacity() const { return space_.capacity(); }
   uint8_t *arena() const { return arena_; }
   cudaStream_t stream() const { return stream_; }
   int cuda_device() const { return cuda_dev_; }
@@ -512,6 +580,25 @@ private:
   uint32_t dcr_get(uint32_t addr) const {
     auto it = dcrs_.find(addr);
     return it == dcrs_.end() ? 0u : it->second;
+  }
+
+  // Which kernel_arg_t the argument block holds: 1 = raycast (layout A, 192 B), 2 = raytracing / RT unit (layout B, 216 B),
+  // 0 = neither.  The reference dispatches by the kernel image; here, in this order: the explicit VX_DCR_B200_RT_LAYOUT; a
+  // host that programmed the RT unit's scene-pointer DCRs 0x006-0x009 (every raytracing host does: tracer.cpp:252-256) is
+  // layout B; an argument buffer of exactly 216 bytes is layout B; anything else of at least 192 bytes is layout A (a raycast
+  // host may allocate its argument buffer with headroom).  `avail` is only a lower-bound check.
+  uint32_t layout_of_locked(uint64_t args_addr, size_t avail) {
+    uint32_t layout = dcr_get(VX_DCR_B200_RT_LAYOUT);
+    if (layout == 0) {
+      const bool rtx_dcrs = dcrs_.count(VX_DCR_BASE_RTX_TLAS_PTR) && dcrs_.count(VX_DCR_BASE_RTX_BVH_PTR);
+      uint64_t start = 0;
+      auto *b = space_.find(args_addr, 1, &start);
+      const bool exact_b = b && b->size - (args_addr - start) == sizeof(KernelArgB);
+      layout = (rtx_dcrs || exact_b) ? 2 : 1;
+    }
+    if (layout == 2 && avail < sizeof(KernelArgB)) return 0;
+    if (layout == 1 && avail < sizeof(KernelArgA)) return 0;
+    return layout <= 2 ? layout : 0;
   }
 
   int fetch_args_locked(uint64_t args_addr, std::vector<uint8_t> &out) {
@@ -582,6 +669,9 @@ private:
     stats_.lane_steps = h_counters_->lane_steps;
     stats_.warp_steps = h_counters_->warp_steps;
     stats_.warps = h_counters_->warps;
+    for (int a = 0; a < 3; a++)
+      for (int b = 0; b < 5; b++) stats_.latency_dist[a][b] = h_counters_->latency[a * 5 + b];
+    for (int a = 0; a < 16; a++) stats_.steps_hist[a] = h_counters_->steps_hist[a];
     if (h_counters_->errors) return fail("run failed on the device (error bits 0x%llx: 1 traversal stack overflow, 2 traceRay nesting too deep, 4 COMMIT_CONT in strict order)", (unsigned long long)h_counters_->errors);
     stats_.kernel_launches = launches_;
     stats_.prep_launches = prep_launches_;
@@ -619,7 +709,10 @@ private:
       if (remote_fb_) {   // store this rank's bands straight into the image owner's framebuffer (peer memory)
         if (remote_bytes_ < (uint64_t)a.dst_width * a.dst_height * 4) return fail("remote framebuffer smaller than the image");
         out = remote_fb_;
+      } else if (peer_fb_arena_) {
+        out = reinterpret_cast<uint32_t *>(peer_fb_arena_ + a.dst_addr);
       }
+      last_out_ = Output{a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, a.dst_width, a.dst_height, true, true};
     } else {
       uint64_t n = rays_addr ? count : (uint64_t)a.dst_width * a.dst_height;
       if (pipe_hits_) {   // chunk of vx_b200_trace_rays_host: staging buffers outside the arena
@@ -627,6 +720,7 @@ private:
       } else {
         if (resolve(*hits_addr, n * sizeof(HitA), 4, "hits", &hits)) return -1;
         if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &rays)) return -1;
+        last_out_ = Output{*hits_addr, n * sizeof(HitA), 0, 0, false, true};
       }
       count = n;
     }
@@ -776,7 +870,10 @@ private:
         rc = launch_trace_machine(p, prop_.multiProcessorCount, stream_);
       }
     }
-    if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    if (rc < 0) {
+      sched_active_ = -1, sched_timed_ = -1;   // no frame ran: nothing to read costs or a trial time from
+      return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    }
     launches_ += rc;
     return end_run_locked();
   }
@@ -845,7 +942,10 @@ private:
     if (remote_fb_) {
       if (remote_bytes_ < (uint64_t)a.dst_width * a.dst_height * 4) return fail("remote framebuffer smaller than the image");
       p.out = remote_fb_;
+    } else if (peer_fb_arena_) {
+      p.out = reinterpret_cast<uint32_t *>(peer_fb_arena_ + a.dst_addr);
     }
+    last_out_ = Output{a.dst_addr, (uint64_t)a.dst_width * a.dst_height * 4, a.dst_width, a.dst_height, true, true};
     if (begin_run_locked() != 0) return -1;
     if (rtu_scene_locked(a, &p.scene)) return -1;
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
@@ -857,7 +957,10 @@ private:
     uint32_t kernel = dcr_get(VX_DCR_B200_RT_KERNEL);
     int rc = kernel >= 2 ? launch_rtu_program(p, kernel - 2, prop_.multiProcessorCount, stream_)
                          : launch_rtu_render(p, prop_.multiProcessorCount, stream_);
-    if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    if (rc < 0) {
+      sched_active_ = -1, sched_timed_ = -1;   // no frame ran: nothing to read costs or a trial time from
+      return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    }
     launches_ += rc;
     return end_run_locked();
   }
@@ -874,6 +977,7 @@ private:
     } else {
       if (resolve(hits_addr, n * sizeof(HitA), 4, "hits", &p.hits)) return -1;
       if (rays_addr && resolve(*rays_addr, n * 24, 4, "rays", &p.rays)) return -1;
+      last_out_ = Output{hits_addr, n * sizeof(HitA), 0, 0, false, true};
     }
     if (begin_run_locked() != 0) return -1;
     if (rtu_scene_locked(a, &p.scene)) return -1;
@@ -881,7 +985,10 @@ private:
     p.arg = a, p.count = n, p.counters = counters_, p.stats = stats_on_;
     p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
     int rc = launch_rtu_trace(p, prop_.multiProcessorCount, stream_);
-    if (rc < 0) return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    if (rc < 0) {
+      sched_active_ = -1, sched_timed_ = -1;   // no frame ran: nothing to read costs or a trial time from
+      return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    }
     launches_ += rc;
     return end_run_locked();
   }
@@ -1032,7 +1139,8 @@ private:
       CUDA_TRY(cudaMalloc(&st.d_cost, st.n_groups * 4));
       CUDA_TRY(cudaMallocHost(&st.h_cost, st.n_groups * 4));
       CUDA_TRY(cudaMallocHost(&st.h_order, st.n_groups * 4));
-      st.order.assign(st.n_groups, 0);
+      st.order.resize(st.n_groups);
+      for (uint32_t i = 0; i < st.n_groups; i++) st.order[i] = i;   // identity until a measured order exists
       memcpy(st.key, key, sizeof(key));
       st.valid = true, st.pending = false, st.use_order = false, st.frames = 0;
     }
@@ -1047,12 +1155,12 @@ private:
         for (uint32_t i = 0; i < st.n_groups; i += 8) fprintf(stderr, " %u", st.h_cost[i]);
         fprintf(stderr, "\n");
       }
+      for (uint32_t i = 0; i < st.n_groups; i++) st.order[i] = i;   // sum == 0 (nothing measured): back to the identity
       if (sum) {
-        for (uint32_t i = 0; i < st.n_groups; i++) st.order[i] = i;
         const uint32_t *c = st.h_cost;
         std::stable_sort(st.order.begin(), st.order.end(), [c](uint32_t a, uint32_t b) { return c[a] > c[b]; });
-        st.order_dirty = true;
       }
+      st.order_dirty = true;
       st.pending = false;
     }
     bool identity;
@@ -1119,6 +1227,11 @@ private:
   void *remote_base_ = nullptr;
   uint32_t *remote_fb_ = nullptr;
   uint64_t remote_bytes_ = 0;
+  uint8_t *peer_fb_arena_ = nullptr;   // same-process owner of the image (DeviceGroup, VORTEX_B200_FB=peer)
+  uint8_t *stage_ = nullptr;           // page-locked ring for small uploads
+  cudaEvent_t stage_ev_[kStageSlots] = {};
+  int stage_next_ = 0;
+  Output last_out_;
   // layout-A GPU triangle records
   GpuTri *gtri_ = nullptr;
   uint64_t gtri_cap_ = 0, gtri_slots_ = 0;
@@ -1143,8 +1256,10 @@ private:
   vx_b200_stats_t stats_{};
 };
 
+#include "vx_group.inc"   // class DeviceGroup: what a vx_device_h points at (one or several Devices)
+
 struct Buffer {   // what a vx_buffer_h points at (reference: callbacks.inc:14-18)
-  Device *device;
+  DeviceGroup *device;
   uint64_t addr;
   uint64_t size;
 };
@@ -1152,7 +1267,7 @@ struct Buffer {   // what a vx_buffer_h points at (reference: callbacks.inc:14-1
 }  // namespace vxb
 
 using vxb::Buffer;
-using vxb::Device;
+using Device = vxb::DeviceGroup;
 using vxb::fail;
 
 // =====================================================================================================
@@ -1353,6 +1468,24 @@ VXB_EXPORT int vx_dump_perf(vx_device_h hdevice, FILE *stream) {
     fprintf(stream, "PERF: rt: warps=%llu, warp_steps=%llu, thread_steps=%llu, simt_efficiency=%.4f, steps_per_ray=%.2f\n",
             (unsigned long long)s.warps, (unsigned long long)s.warp_steps, (unsigned long long)s.lane_steps,
             (double)s.lane_steps / (32.0 * (double)s.warp_steps), s.rays ? (double)s.lane_steps / (double)s.rays : 0.0);
+  // RTUnit::print_stats' latency table (sim/simx/rt_unit.cpp:265-292): per warp status, what its lanes were doing
+  uint64_t any = 0;
+  for (int a = 0; a < 3; a++)
+    for (int b = 0; b < 5; b++) any += s.latency_dist[a][b];
+  if (any) {
+    static const char *wn[3] = {"warp_fetching_work", "warp_shading", "warp_traversing"};
+    static const char *rn[5] = {"awaiting_processing", "awaiting_scheduling", "awaiting_mf", "executing_op", "trace_complete"};
+    for (int a = 0; a < 3; a++) {
+      fprintf(stream, "PERF: rt: %s:", wn[a]);
+      for (int b = 0; b < 5; b++) fprintf(stream, " %s=%.2f%%", rn[b], 100.0 * (double)s.latency_dist[a][b] / (double)any);
+      fprintf(stream, "\n");
+    }
+    fprintf(stream, "PERF: rt: steps_per_ray_log2_hist:");
+    for (int a = 0; a < 16; a++) fprintf(stream, " %llu", (unsigned long long)s.steps_hist[a]);
+    fprintf(stream, "\n");
+  }
+  if (s.gpus > 1)
+    fprintf(stream, "PERF: gpus=%u, group_ms=%.4f, kernel_ms fastest/slowest GPU = %.4f / %.4f\n", s.gpus, s.group_ms, s.kernel_ms_min, s.kernel_ms_max);
   return 0;
 }
 
@@ -1390,6 +1523,20 @@ VXB_EXPORT int vx_dev_init(callbacks_t *cb) {
 VXB_EXPORT int vx_b200_select_device(int cuda_device) {
   vxb::g_selected_device = cuda_device;
   return 0;
+}
+VXB_EXPORT int vx_b200_select_gpus(int n_gpus) {
+  vxb::g_selected_gpus = n_gpus;
+  return 0;
+}
+VXB_EXPORT int vx_b200_set_readback(vx_device_h h, vx_buffer_h hframebuffer, void *host_ptr, uint64_t bytes) {
+  if (!h || !hframebuffer) return -1;
+  auto b = (Buffer *)hframebuffer;
+  if (host_ptr && bytes > b->size) return fail("vx_b200_set_readback: more bytes than the framebuffer holds");
+  return ((Device *)h)->set_readback(b->addr, host_ptr, bytes);
+}
+VXB_EXPORT int vx_b200_flush_l2(vx_device_h h) {
+  if (!h) return -1;
+  return ((Device *)h)->flush_l2();
 }
 VXB_EXPORT int vx_b200_set_partition(vx_device_h h, uint32_t rank, uint32_t world, uint32_t band_rows) {
   if (!h) return -1;
@@ -1445,6 +1592,7 @@ VXB_EXPORT int vx_b200_probe_gather(vx_device_h h, uint64_t buffer_bytes, uint32
 VXB_EXPORT int vx_b200_device_ptr(vx_buffer_h hbuffer, uint64_t *cuda_ptr) {
   if (!hbuffer || !cuda_ptr) return -1;
   auto b = (Buffer *)hbuffer;
+  if (b->device->make_resident(b->addr) != 0) return -1;   // several GPUs: the pieces of a kernel output are gathered on GPU 0 first
   *cuda_ptr = (uint64_t)(uintptr_t)(b->device->arena() + b->addr);
   return 0;
 }

@@ -29,12 +29,12 @@ CAMERA_FIXED, CAMERA_PINHOLE = 0, 1   # kernel.cpp:28-39 (what the shipped kerne
 
 
 class RtxTracer:
-    def __init__(self, width, height, spp=1, max_depth=1, cuda_device=None):
+    def __init__(self, width, height, spp=1, max_depth=1, cuda_device=None, gpus=None):
         self.width, self.height = int(width), int(height)
         self.karg = np.zeros(1, dtype=KARG_B_DT)
         self.karg["dst_width"], self.karg["dst_height"] = self.width, self.height
         self.karg["samples_per_pixel"], self.karg["max_depth"] = spp, max_depth
-        self.dev = vx.Device(cuda_device)
+        self.dev = vx.Device(cuda_device, gpus=gpus)
         self.bufs, self.shaders = {}, []
         self.krnl = self.out = self.args = self.sbt = None
 

@@ -30,12 +30,12 @@ _ADDR_FIELD = {"tri": "tri_addr", "triEx": "triEx_addr", "triIdx": "triIdx_addr"
 
 
 class Tracer:
-    def __init__(self, width, height, spp=1, max_depth=1, cuda_device=None):
+    def __init__(self, width, height, spp=1, max_depth=1, cuda_device=None, gpus=None):
         self.width, self.height = int(width), int(height)
         self.karg = np.zeros(1, dtype=KARG_DT)
         self.karg["dst_width"], self.karg["dst_height"] = self.width, self.height
         self.karg["samples_per_pixel"], self.karg["max_depth"] = spp, max_depth
-        self.dev = vx.Device(cuda_device)
+        self.dev = vx.Device(cuda_device, gpus=gpus)
         self.bufs = {}
         self.krnl = None
         self.out = None

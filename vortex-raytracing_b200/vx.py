@@ -24,7 +24,7 @@ EXPORTS = (
     "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
-    "vx_b200_select_device vx_b200_set_partition vx_b200_build_bvh vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_mark_written vx_b200_probe_gather vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_select_device vx_b200_select_gpus vx_b200_set_readback vx_b200_flush_l2 vx_b200_set_partition vx_b200_build_bvh vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_mark_written vx_b200_probe_gather vx_b200_stream vx_b200_last_kernel_ms "
     "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_trace_rays_host vx_b200_last_error"
 ).split()
 
@@ -37,7 +37,9 @@ class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64), ("blas_entered", C.c_uint64),
                 ("shaded_hits", C.c_uint64), ("kernel_launches", C.c_uint64), ("prep_launches", C.c_uint64),
                 ("kernel_ms", C.c_float), ("prep_ms", C.c_float),
-                ("lane_steps", C.c_uint64), ("warp_steps", C.c_uint64), ("warps", C.c_uint64)]
+                ("lane_steps", C.c_uint64), ("warp_steps", C.c_uint64), ("warps", C.c_uint64),
+                ("gpus", C.c_uint32), ("group_ms", C.c_float), ("kernel_ms_min", C.c_float), ("kernel_ms_max", C.c_float),
+                ("latency_dist", (C.c_uint64 * 5) * 3), ("steps_hist", C.c_uint64 * 16)]
 
 
 _lib = None
@@ -61,7 +63,8 @@ def lib():
             "vx_dcr_read": [H, u32, C.POINTER(u32)], "vx_dcr_write": [H, u32, u32], "vx_mpm_query": [H, u32, u32, C.POINTER(u64)],
             "vx_upload_kernel_bytes": [H, vp, u64, C.POINTER(B)], "vx_upload_kernel_file": [H, C.c_char_p, C.POINTER(B)],
             "vx_upload_bytes": [H, vp, u64, C.POINTER(B)], "vx_upload_file": [H, C.c_char_p, C.POINTER(B)],
-            "vx_b200_select_device": [i32], "vx_b200_set_partition": [H, u32, u32, u32], "vx_b200_device_ptr": [B, C.POINTER(u64)], "vx_b200_mark_written": [B], "vx_b200_probe_gather": [H, u64, u32, C.POINTER(C.c_double)],
+            "vx_b200_select_device": [i32], "vx_b200_select_gpus": [i32], "vx_b200_set_readback": [H, B, vp, u64], "vx_b200_flush_l2": [H],
+            "vx_b200_set_partition": [H, u32, u32, u32], "vx_b200_device_ptr": [B, C.POINTER(u64)], "vx_b200_mark_written": [B], "vx_b200_probe_gather": [H, u64, u32, C.POINTER(C.c_double)],
             "vx_b200_stream": [H, C.POINTER(u64)], "vx_b200_last_kernel_ms": [H, C.POINTER(C.c_float)],
             "vx_b200_enable_stats": [H, i32], "vx_b200_get_stats": [H, C.POINTER(Stats)],
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
@@ -142,12 +145,17 @@ class Buffer:
 class Device:
     """vx_device_h with the reference's call names as methods."""
 
-    def __init__(self, cuda_device=None):
+    def __init__(self, cuda_device=None, gpus=None):
+        """gpus: how many GPUs of the box this ONE device handle spans (vx_b200_select_gpus; default env VORTEX_B200_GPUS, else 1)"""
         L = lib()
         if cuda_device is not None:
             L.vx_b200_select_device(int(cuda_device))
+        L.vx_b200_select_gpus(int(gpus) if gpus else 0)
         h = C.c_void_p()
-        _check(L.vx_dev_open(C.byref(h)), "vx_dev_open")
+        try:
+            _check(L.vx_dev_open(C.byref(h)), "vx_dev_open")
+        finally:
+            L.vx_b200_select_gpus(0)
         self.h = h
 
     def close(self):
@@ -260,7 +268,19 @@ class Device:
     def stats(self):
         s = Stats()
         _check(lib().vx_b200_get_stats(self.h, C.byref(s)), "vx_b200_get_stats")
-        return {n: getattr(s, n) for n, _ in Stats._fields_}
+        out = {n: getattr(s, n) for n, _ in Stats._fields_}
+        out["latency_dist"] = [[int(v) for v in row] for row in s.latency_dist]
+        out["steps_hist"] = [int(v) for v in s.steps_hist]
+        return out
+
+    def set_readback(self, framebuffer, host_ptr, nbytes):
+        """every later vx_start of `framebuffer` ends with the copy of the image into pinned host memory at `host_ptr`
+        (each GPU copies its own bands); None cancels"""
+        _check(lib().vx_b200_set_readback(self.h, framebuffer.h, C.c_void_p(host_ptr) if host_ptr else None, C.c_uint64(nbytes)),
+               "vx_b200_set_readback")
+
+    def flush_l2(self):
+        _check(lib().vx_b200_flush_l2(self.h), "vx_b200_flush_l2")
 
     def trace_primary(self, arguments, hits):
         _check(lib().vx_b200_trace_primary(self.h, arguments.h, hits.h), "vx_b200_trace_primary")
