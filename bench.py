@@ -493,6 +493,11 @@ def measure_incoherent(name, gpus, steps, warmup, cpu=False, clocks=False):
     tracer_mod, scenes = pkg("tracer"), pkg("scenes")
     wl = WORKLOADS[name]
     R = int(wl["rays_per_gpu"]) * gpus
+    # every GPU's arena mirrors the whole address space (scene + the ray and hit buffers of ALL GPUs): beyond the 4 GiB of the
+    # XLEN=32 build the backend is asked for a larger arena (addresses above 4 GiB are fine for layout A's 64-bit fields)
+    need_gb = (R * 48 + 170 * 2 * wl["n"] ** 2) / 2 ** 30 + 0.5
+    if need_gb > 4:
+        os.environ["VORTEX_B200_MEM_GB"] = str(int(need_gb) + 1)
     hs, build_s = host_scene(wl)
     karg = hs.setup(wl["w"], wl["h"], spp=1, max_depth=1)
     bufs = hs.buffers()
@@ -593,6 +598,7 @@ def measure_incoherent(name, gpus, steps, warmup, cpu=False, clocks=False):
     rb.free()
     hb.free()
     tr.close()
+    os.environ.pop("VORTEX_B200_MEM_GB", None)
     ntri = 2 * wl["n"] ** 2
     return {"workload": name, "baseline_config_index": wl["config_index"], "value": value, "unit": "Mrays/s", "n_gpus": gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": total_ms / steps, "rays_per_step": R, "triangles": ntri, "scene_scale": wl.get("scale", 1.0),

@@ -97,6 +97,26 @@ __device__ __forceinline__ bool slab_hit(float4 lo, float4 hi, f3 o, f3 id, bool
   return !(tmax < tmin || tmax <= 0) && (tmin < limit);
 }
 
+// A/B variant (-DVXB_SLAB_FMA=1, fast order's 4-wide records only; NOT the default): the slab planes as one FFMA each,
+// t = plane * id - o * id, on boxes padded outward by kSlabPadUlps ulps when the records are built.  It is NOT the reference's
+// arithmetic (one rounding instead of two, a different cancellation), so it can accept or reject a grazing box the reference
+// decides the other way: the hit then still comes from the exact Moller-Trumbore test, but the set of triangles reached may
+// differ from the reference's own false negatives.  Measured against the exact test in profiles/r02_sweep_slab_fma.txt.
+#ifndef VXB_SLAB_FMA
+#define VXB_SLAB_FMA 0
+#endif
+constexpr int kSlabPadUlps = 2;
+__device__ __forceinline__ bool slab_hit_fma(float lox, float loy, float loz, float hix, float hiy, float hiz, f3 id, f3 noid, float limit,
+                                             float &tmin_out) {
+  float tx1 = __fmaf_rn(lox, id.x, noid.x), tx2 = __fmaf_rn(hix, id.x, noid.x);
+  float ty1 = __fmaf_rn(loy, id.y, noid.y), ty2 = __fmaf_rn(hiy, id.y, noid.y);
+  float tz1 = __fmaf_rn(loz, id.z, noid.z), tz2 = __fmaf_rn(hiz, id.z, noid.z);
+  float tmin = fmaxf(fmaxf(fminf(tx1, tx2), fminf(ty1, ty2)), fminf(tz1, tz2));
+  float tmax = fminf(fminf(fmaxf(tx1, tx2), fmaxf(ty1, ty2)), fmaxf(tz1, tz2));
+  tmin_out = tmin;
+  return !(tmax < tmin || tmax <= 0) && (tmin < limit);
+}
+
 // ---- ray_t::intersect(tri) (geometry.h:1416-1445), triangle in edge form ----
 __device__ __forceinline__ bool moller_trumbore(const Ray &r, f3 v0, f3 e1, f3 e2, float &t, float &w1o, float &w2o) {
   f3 h = cross3(r.d, e2);

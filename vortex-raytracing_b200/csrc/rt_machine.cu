@@ -167,6 +167,21 @@ __device__ __forceinline__ void step_wide(Lane &L, bool careful, uint32_t *stk_e
   float d[4];
   uint32_t e[4] = {ds.x, ds.y, ds.z, ds.w};
   const float kInf = __int_as_float(0x7F800000);
+#if VXB_SLAB_FMA
+  if (!careful) {
+    const f3 noid = mk3(-(L.o.x * L.id.x), -(L.o.y * L.id.y), -(L.o.z * L.id.z));
+    float t;
+    bool h;
+    h = slab_hit_fma(lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, L.id, noid, L.dist, t);
+    d[0] = h ? t : kInf;
+    h = slab_hit_fma(lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, L.id, noid, L.dist, t);
+    d[1] = h ? t : kInf;
+    h = slab_hit_fma(lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, L.id, noid, L.dist, t);
+    d[2] = h ? t : kInf;
+    h = slab_hit_fma(lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, L.id, noid, L.dist, t);
+    d[3] = h ? t : kInf;
+  } else
+#endif
   {
     float t;
     bool h;

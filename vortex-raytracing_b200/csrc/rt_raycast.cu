@@ -415,6 +415,11 @@ __global__ void k_build_wide(const uint8_t *__restrict__ nodes, uint64_t n_nodes
   auto put = [&](uint32_t local) {                                       // child `local` (instance-local index) becomes a slot
     const uint8_t *c = nodes + (base + local) * sizeof(BvhNodeA);
     float4 c0 = ldg4(c), c1 = ldg4(c + 16);
+#if VXB_SLAB_FMA   // A/B variant: boxes padded outward for the one-rounding slab test (rt_device.cuh)
+    auto down = [](float v) { for (int k = 0; k < kSlabPadUlps; ++k) v = nextafterf(v, -INFINITY); return v; };
+    auto up = [](float v) { for (int k = 0; k < kSlabPadUlps; ++k) v = nextafterf(v, INFINITY); return v; };
+    c0.x = down(c0.x), c0.y = down(c0.y), c0.z = down(c0.z), c1.x = up(c1.x), c1.y = up(c1.y), c1.z = up(c1.z);
+#endif
     w.lox[slot] = c0.x, w.loy[slot] = c0.y, w.loz[slot] = c0.z;
     w.hix[slot] = c1.x, w.hiy[slot] = c1.y, w.hiz[slot] = c1.z;
     w.desc[slot] = wide_desc(__float_as_uint(c0.w), __float_as_uint(c1.w), local);

@@ -9,6 +9,8 @@
 #include <dlfcn.h>
 
 #include <chrono>
+#include <condition_variable>
+#include <functional>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -27,6 +29,7 @@
 #include "rt_rtu.h"
 #include "rt_build.h"
 #include "rt_probe.h"
+#include "rt_xfer.h"
 #include <algorithm>
 
 #define VXB_EXPORT extern "C" __attribute__((visibility("default")))
