@@ -43,6 +43,20 @@ constexpr uint32_t F_ANY = 4, F_NAN = 8, F_INBLAS = 16, F_OCCL = 32;
 #ifndef VXB_MIN_BLOCKS
 #define VXB_MIN_BLOCKS 4
 #endif
+// A/B variant (-DVXB_SMEM_TOP=1, NOT the default; north_star lists "BVH top levels staged in shared memory" as a candidate):
+// every CTA copies the first three levels of the 4-wide tree of a single-instance scene (<= 21 records, 2.7 KB) into shared
+// memory and re-labels the cursors between them, so that visits of those records read shared memory instead of L1.
+// Measured in profiles/r02_sweep_smem_top.txt.
+#ifndef VXB_SMEM_TOP
+#define VXB_SMEM_TOP 0
+#endif
+// ... measured: frames lose 2 % (the staged records are the lines L1 keeps anyway, and generic loads replace ld.global.nc),
+// incoherent rays gain 6 % without the stack ring below and lose 1 % with it (profiles/r02_sweep_trace_ring_top.txt): off
+#ifndef VXB_TRACE_TOP
+#define VXB_TRACE_TOP 0
+#endif
+constexpr uint32_t kTopTag = 1u << 26;   // inner cursor whose payload is a slot of the staged tree top
+constexpr uint32_t kTopSlots = 21;
 
 // shared-memory columns (one 32-bit word per thread each)
 enum : uint32_t {
@@ -61,6 +75,7 @@ struct Lane {
   uint32_t cur, sp, st;
   uint32_t blas;
   uint32_t steps;         // statistics builds: traversal steps of the ray in this slot
+  uint32_t base;          // -DVXB_SMEM_STACK: entries below this index are in local memory, [base, sp) in the shared-memory ring
   const uint8_t *nodes;   // first node of the instance being traversed
   const uint8_t *wide;    // its 4-wide records (fast order), same node indexing
 };
@@ -97,6 +112,7 @@ __device__ __forceinline__ void start_ray(Lane &L, const Smem &sm, const SceneA 
   L.dist = tmax, L.bx = 0.f, L.by = 0.f, L.hblas = 0, L.htri = 0;
   L.cur = kTlasTag | sc.tlas_root;
   L.sp = 0;
+  L.base = 0;
   L.steps = 0;
   lc.rays++;
 }
@@ -112,23 +128,75 @@ __device__ __forceinline__ void lat_note(uint32_t *lat, uint32_t row, uint32_t s
   }
 }
 
-template <bool STRICT>
-__device__ __forceinline__ void pop(Lane &L, const uint32_t *stk_e, const float *stk_d) {
+// The traversal stack: entries (cursor, entry distance) in local memory.  A/B variant -DVXB_SMEM_STACK=K (NOT the default): the
+// newest K entries live in a shared-memory ring (one uint2 column per thread, conflict-free), older ones are written back to
+// the local-memory arrays when the ring is full and read from there once the ring has drained — the stack's hot end then no
+// longer competes with node records for L1 lines.  Measured in profiles/r02_sweep_smem_stack.txt.
+#ifndef VXB_SMEM_STACK
+#define VXB_SMEM_STACK 0
+#endif
+// ... measured: frames lose 3-6 % with K = 8 (shared memory taken from L1, coherent rays keep their stack lines hot anyway),
+// incoherent rays gain 13 % (K = 8) / 10 % (K = 16): the hit-record mode uses the ring by default
+#ifndef VXB_TRACE_RING
+#define VXB_TRACE_RING 8
+#endif
+struct Stk {
+  uint32_t *e;
+  float *d;
+  uint2 *ring;   // [VXB_SMEM_STACK][kBlockThreads], this thread's column already applied
+};
+template <int RING>
+__device__ __forceinline__ void stk_push(Lane &L, const Stk &s, uint32_t e, float d) {
+  if (RING > 0) {
+    constexpr uint32_t K = RING > 0 ? RING : 1;
+    if (L.sp - L.base == K) {   // ring full: its oldest entry goes to local memory
+      const uint2 o = s.ring[(L.base % K) * kBlockThreads];
+      s.e[L.base] = o.x, s.d[L.base] = __uint_as_float(o.y);
+      ++L.base;
+    }
+    s.ring[(L.sp % K) * kBlockThreads] = make_uint2(e, __float_as_uint(d));
+  } else {
+    s.e[L.sp] = e, s.d[L.sp] = d;
+  }
+  ++L.sp;
+}
+template <int RING>
+__device__ __forceinline__ void stk_pop(Lane &L, const Stk &s, uint32_t &e, float &d) {   // L.sp > 0
+  --L.sp;
+  if (RING > 0) {
+    constexpr uint32_t K = RING > 0 ? RING : 1;
+    if (L.sp < L.base) {   // the ring has drained: older entries are in local memory
+      L.base = L.sp;
+      e = s.e[L.sp], d = s.d[L.sp];
+    } else {
+      const uint2 o = s.ring[(L.sp % K) * kBlockThreads];
+      e = o.x, d = __uint_as_float(o.y);
+    }
+  } else {
+    e = s.e[L.sp], d = s.d[L.sp];
+  }
+}
+
+template <bool STRICT, int RING>
+__device__ __forceinline__ void pop(Lane &L, const Stk &stk) {
+  uint32_t e;
+  float d;
   if (STRICT) {   // the reference never re-tests a pushed node (render.h:82-83, :151-152)
     if (L.sp == 0) { L.st = (L.st & ~S_MASK) | S_DONE; return; }
-    L.cur = stk_e[--L.sp];
+    stk_pop<RING>(L, stk, e, d);
+    L.cur = e;
   } else {
     for (;;) {
       if (L.sp == 0) { L.st = (L.st & ~S_MASK) | S_DONE; return; }
-      --L.sp;
-      if (stk_d[L.sp] < L.dist) { L.cur = stk_e[L.sp]; return; }
+      stk_pop<RING>(L, stk, e, d);
+      if (d < L.dist) { L.cur = e; return; }
     }
   }
 }
 
 // one inner-node visit inside an instance: both children are one 64-byte record (render.h:100-124)
-template <bool STRICT, bool STATS>
-__device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool careful, uint32_t *stk_e, float *stk_d, Local &lc) {
+template <bool STRICT, bool STATS, int RING>
+__device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool careful, const Stk &stk, Local &lc) {
   uint32_t first = L.cur;   // kind bits are zero for an inner pair
   const uint8_t *pair = L.nodes + (size_t)first * sizeof(BvhNodeA);
   float4 l0 = ldg4(pair), l1 = ldg4(pair + 16), r0 = ldg4(pair + 32), r1 = ldg4(pair + 48);
@@ -141,9 +209,7 @@ __device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool caref
   if (hitL && hitR) {
     bool right_next = STRICT ? (dL < dR) : (dR < dL);   // STRICT: the reference visits the FARTHER child first (render.h:113-118)
     if (L.sp < kMachineStack) {
-      stk_e[L.sp] = right_next ? eL : eR;
-      if (!STRICT) stk_d[L.sp] = right_next ? dL : dR;
-      ++L.sp;
+      stk_push<RING>(L, stk, right_next ? eL : eR, right_next ? dL : dR);
     } else {
       lc.err |= 1u;
     }
@@ -153,17 +219,26 @@ __device__ __forceinline__ void step_inner(Lane &L, const SceneA &sc, bool caref
   } else if (hitR) {
     L.cur = eR;
   } else {
-    pop<STRICT>(L, stk_e, stk_d);
+    pop<STRICT, RING>(L, stk);
   }
 }
 
 // one visit of a 4-wide record (GpuNode4): the cursor's payload is the inner BVH2 node whose grandchildren are tested.
 // Nearest slot next, the others pushed farthest first; every pushed entry carries its entry distance for the re-cull at pop.
-template <bool STATS>
-__device__ __forceinline__ void step_wide(Lane &L, bool careful, uint32_t *stk_e, float *stk_d, Local &lc) {
-  const uint8_t *w = L.wide + (size_t)L.cur * sizeof(GpuNode4);
-  float4 lox = ldg4(w), loy = ldg4(w + 16), loz = ldg4(w + 32), hix = ldg4(w + 48), hiy = ldg4(w + 64), hiz = ldg4(w + 80);
-  uint4 ds = __ldg(reinterpret_cast<const uint4 *>(w + 96));
+template <bool STATS, int RING, bool TOP>
+__device__ __forceinline__ void step_wide(Lane &L, bool careful, const Stk &stk, Local &lc, const uint8_t *top) {
+  float4 lox, loy, loz, hix, hiy, hiz;
+  uint4 ds;
+  if (TOP) {   // generic loads: lanes of one warp may read shared memory and global memory in the same instruction
+    const uint8_t *w = (L.cur & kTopTag) ? top + (size_t)(L.cur & 31u) * sizeof(GpuNode4) : L.wide + (size_t)L.cur * sizeof(GpuNode4);
+    const float4 *wv = reinterpret_cast<const float4 *>(w);
+    lox = wv[0], loy = wv[1], loz = wv[2], hix = wv[3], hiy = wv[4], hiz = wv[5];
+    ds = *reinterpret_cast<const uint4 *>(w + 96);
+  } else {
+    const uint8_t *w = L.wide + (size_t)L.cur * sizeof(GpuNode4);
+    lox = ldg4(w), loy = ldg4(w + 16), loz = ldg4(w + 32), hix = ldg4(w + 48), hiy = ldg4(w + 64), hiz = ldg4(w + 80);
+    ds = __ldg(reinterpret_cast<const uint4 *>(w + 96));
+  }
   float d[4];
   uint32_t e[4] = {ds.x, ds.y, ds.z, ds.w};
   const float kInf = __int_as_float(0x7F800000);
@@ -214,21 +289,21 @@ __device__ __forceinline__ void step_wide(Lane &L, bool careful, uint32_t *stk_e
 #undef VXB_CSWAP
   if (d[0] < kInf) {
     if (L.sp + 3 <= kMachineStack) {
-      if (d[3] < kInf) { stk_e[L.sp] = e[3]; stk_d[L.sp] = d[3]; ++L.sp; }
-      if (d[2] < kInf) { stk_e[L.sp] = e[2]; stk_d[L.sp] = d[2]; ++L.sp; }
-      if (d[1] < kInf) { stk_e[L.sp] = e[1]; stk_d[L.sp] = d[1]; ++L.sp; }
+      if (d[3] < kInf) stk_push<RING>(L, stk, e[3], d[3]);
+      if (d[2] < kInf) stk_push<RING>(L, stk, e[2], d[2]);
+      if (d[1] < kInf) stk_push<RING>(L, stk, e[1], d[1]);
     } else {
       lc.err |= 1u;   // stack overflow: vx_ready_wait reports the run as failed
     }
     L.cur = e[0];
   } else {
-    pop<false>(L, stk_e, stk_d);
+    pop<false, RING>(L, stk);
   }
 }
 
 // everything that is not an inner-node pair: leaves, nodes that must be read first, TLAS nodes / instance entry
-template <bool STRICT, bool STATS>
-__device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA &sc, uint32_t *stk_e, float *stk_d, Local &lc) {
+template <bool STRICT, bool STATS, int RING, bool TOP>
+__device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA &sc, const Stk &stk, Local &lc, bool top_staged) {
   if (L.cur & kTlasTag) {
     if (L.st & F_INBLAS) {   // back from an instance: the active ray becomes the world-space ray again
       L.o = sm.get3(C_WOX), L.d = sm.get3(C_WDX);
@@ -267,9 +342,7 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       if (hitL && hitR) {   // near child first at this level (render.h:175-180)
         bool swap = dL > dR;
         if (L.sp < kMachineStack) {
-          stk_e[L.sp] = kTlasTag | (swap ? left : right);
-          if (!STRICT) stk_d[L.sp] = swap ? dL : dR;
-          ++L.sp;
+          stk_push<RING>(L, stk, kTlasTag | (swap ? left : right), swap ? dL : dR);
         } else {
           lc.err |= 1u;
         }
@@ -279,7 +352,7 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       } else if (hitR) {
         L.cur = kTlasTag | right;
       } else {
-        pop<STRICT>(L, stk_e, stk_d);
+        pop<STRICT, RING>(L, stk);
       }
     }
     return;
@@ -293,7 +366,7 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       // monotonic, so a ray that fails here fails both children too — rejecting it now skips only failing tests
       float t0;
       if (!slab_hit(a, b, L.o, L.id, (L.st & F_NAN) != 0, L.dist, t0)) {
-        pop<STRICT>(L, stk_e, stk_d);
+        pop<STRICT, RING>(L, stk);
         return;
       }
     }
@@ -301,6 +374,7 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
     count = __float_as_uint(b.w);
     if (count == 0) {   // an inner node after all: visited by the inner loop (its child pair, or its 4-wide record)
       L.cur = STRICT ? (first & kPay) : (L.cur & kPay);
+      if (TOP && !STRICT && top_staged && L.cur == 0u) L.cur = kTopTag;   // the root's record sits in slot 0
       return;
     }
   }
@@ -322,15 +396,15 @@ __device__ __forceinline__ void step_other(Lane &L, const Smem &sm, const SceneA
       L.htri = __float_as_uint(q0.w);
     }
   }
-  pop<STRICT>(L, stk_e, stk_d);
+  pop<STRICT, RING>(L, stk);
 }
 
 __device__ __forceinline__ bool is_inner(const Lane &L) { return (L.st & S_MASK) == S_TRAV && (L.cur >> kKindShift) == 0u; }
 
 // TRAV: runs until fewer than `quorum` lanes of the warp are still traversing
-template <bool STRICT, bool STATS, bool COST>
-__device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &sc, uint32_t quorum, uint32_t inner_quorum, uint32_t *stk_e,
-                                         float *stk_d, Local &lc, uint32_t *lat, bool exhausted) {
+template <bool STRICT, bool STATS, bool COST, int RING, bool TOP>
+__device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &sc, uint32_t quorum, uint32_t inner_quorum, const Stk &stk,
+                                         Local &lc, uint32_t *lat, bool exhausted, const uint8_t *top) {
   for (;;) {
     // warp-uniform choice of the NaN-exact min/max path (no divergence); F_NAN only changes in step_other / start_ray
     const bool careful = __any_sync(0xffffffffu, (L.st & (S_MASK | F_NAN)) == (S_TRAV | F_NAN));
@@ -343,8 +417,8 @@ __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &
         simt_step<STATS>(lc);
         if (STATS) L.steps++;
         if (COST) sm.u(C_T0) += 1u;
-        if (STRICT) step_inner<STRICT, STATS>(L, sc, careful, stk_e, stk_d, lc);   // the reference's own BVH2 walk
-        else step_wide<STATS>(L, careful, stk_e, stk_d, lc);                        // 4-wide records (the launch guarantees sc.wide)
+        if (STRICT) step_inner<STRICT, STATS, RING>(L, sc, careful, stk, lc);   // the reference's own BVH2 walk
+        else step_wide<STATS, RING, TOP>(L, careful, stk, lc, top);                   // 4-wide records (the launch guarantees sc.wide)
       }
     }
     lat_note<STATS>(lat, 2, L.st, (L.st & S_MASK) == S_TRAV && !is_inner(L), exhausted);
@@ -352,7 +426,7 @@ __device__ __forceinline__ void traverse(Lane &L, const Smem &sm, const SceneA &
       simt_step<STATS>(lc);
       if (STATS) L.steps++;
       if (COST) sm.u(C_T0) += 1u;
-      step_other<STRICT, STATS>(L, sm, sc, stk_e, stk_d, lc);
+      step_other<STRICT, STATS, RING, TOP>(L, sm, sc, stk, lc, top != nullptr);
     }
     unsigned t = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_TRAV);
     if ((uint32_t)__popc(t) < quorum) return;
@@ -512,6 +586,10 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   __shared__ float s_cols[kCols * kBlockThreads];
   uint32_t stk_e[kMachineStack];
   float stk_d[kMachineStack];
+  constexpr int RING = (MODE == kModeTrace) ? VXB_TRACE_RING : VXB_SMEM_STACK;
+  constexpr bool TOP = !STRICT && ((MODE == kModeTrace) ? VXB_TRACE_TOP : VXB_SMEM_TOP) != 0;
+  extern __shared__ uint2 s_ring[];   // RING * kBlockThreads entries (dynamic: beyond the 48 KB static limit)
+  const Stk stk{stk_e, stk_d, RING > 0 ? s_ring + threadIdx.x : nullptr};
   const Smem sm{s_cols, threadIdx.x};
   const KernelArgA &a = p.arg;
   const uint32_t lane = threadIdx.x & 31;
@@ -526,13 +604,33 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   if (MODE == kModeTrace) f.total = (uint32_t)((p.count + 31u) / 32u * 32u);
 
   Lane L;
-  L.st = S_EMPTY, L.sp = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.wide = reinterpret_cast<const uint8_t *>(p.scene.wide), L.blas = 0;
+  L.st = S_EMPTY, L.sp = 0, L.base = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.wide = reinterpret_cast<const uint8_t *>(p.scene.wide), L.blas = 0;
   L.o = L.d = L.id = mk3(0, 0, 0);
   L.steps = 0;
   Local lc{0, 0, 0, 0, 0};
   uint32_t lat[STATS ? 15 : 1];
   if (STATS)
     for (int k = 0; k < 15; ++k) lat[k] = 0;
+  const uint8_t *top = nullptr;
+  __shared__ __align__(128) GpuNode4 s_top[TOP ? kTopSlots : 1];
+  if (TOP && p.scene.wide && p.n_blas == 1) {   // warp-uniform: launch parameters only
+    const uint32_t t = threadIdx.x;
+    auto inner = [](uint32_t d) { return d != 0xFFFFFFFFu && (d >> kKindShift) == 0u; };
+    if (t == 0) s_top[0] = p.scene.wide[0];
+    __syncthreads();
+    uint32_t d1 = t < 4 ? s_top[0].desc[t] : 0xFFFFFFFFu;
+    if (t < 4 && inner(d1)) s_top[1 + t] = p.scene.wide[d1];
+    __syncthreads();
+    if (t < 4 && inner(d1)) s_top[0].desc[t] = kTopTag | (1 + t);
+    uint32_t d2 = 0xFFFFFFFFu;
+    __syncthreads();
+    if (t < 16 && (s_top[0].desc[t / 4] & kTopTag) && (s_top[0].desc[t / 4] >> kKindShift) == 0u) d2 = s_top[1 + t / 4].desc[t % 4];
+    if (t < 16 && inner(d2) && !(d2 & kTopTag)) s_top[5 + t] = p.scene.wide[d2];
+    __syncthreads();
+    if (t < 16 && inner(d2) && !(d2 & kTopTag)) s_top[1 + t / 4].desc[t % 4] = kTopTag | (5 + t);
+    __syncthreads();
+    top = reinterpret_cast<const uint8_t *>(s_top);
+  }
   uint32_t chunk_next = 0, chunk_end = 0;
   bool exhausted = (f.total == 0);
 
@@ -541,7 +639,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
     unsigned done = __ballot_sync(0xffffffffu, (L.st & S_MASK) == S_DONE);
     const uint32_t quorum = exhausted ? 1u : p.quorum_refill;
     if (trav && ((uint32_t)__popc(trav) >= quorum || (!done && exhausted))) {
-      traverse<STRICT, STATS, COST>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk_e, stk_d, lc, lat, exhausted);
+      traverse<STRICT, STATS, COST, RING, TOP>(L, sm, p.scene, quorum, exhausted ? 1u : p.quorum_inner, stk, lc, lat, exhausted, top);
       continue;
     }
     if (done) {
@@ -617,11 +715,14 @@ int launch_m(const RenderA &p, int num_sms, cudaStream_t stream) {
   // the cost-recording build runs only on the frames that re-measure the schedule (p.sched.cost set), and never for rays
   auto kern = (MODE != kModeTrace && p.sched.cost) ? k_render_m<MODE, STRICT, STATS, MODE != kModeTrace> : k_render_m<MODE, STRICT, STATS, false>;
   int per_sm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, 0);
+  const size_t dyn = (size_t)((MODE == kModeTrace) ? VXB_TRACE_RING : VXB_SMEM_STACK) * kBlockThreads * sizeof(uint2);
+  cudaError_t e = cudaSuccess;
+  if (dyn) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, dyn);
   if (e != cudaSuccess) return -(int)e;
   if (per_sm < 1) per_sm = 1;
   if (p.blocks_per_sm_cap && per_sm > (int)p.blocks_per_sm_cap) per_sm = (int)p.blocks_per_sm_cap;
-  kern<<<num_sms * per_sm, kBlockThreads, 0, stream>>>(p);
+  kern<<<num_sms * per_sm, kBlockThreads, dyn, stream>>>(p);
   e = cudaGetLastError();
   return e == cudaSuccess ? 1 : -(int)e;
 }

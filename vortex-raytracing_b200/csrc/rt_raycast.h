@@ -76,6 +76,7 @@ struct RenderA {
   HitA *hits;
   uint64_t count;
   const uint32_t *perm;     // hit-record mode: work item k traces ray perm[k] (launch_ray_order), or nullptr = identity
+  uint32_t n_blas;          // instances in the blas buffer (the -DVXB_SMEM_TOP=1 A/B variant stages the tree top only for one)
 };
 
 struct TraceA {

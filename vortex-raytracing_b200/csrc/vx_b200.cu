@@ -745,12 +745,14 @@ private:
     }
     sc.gtri = gtri_;
     sc.wide = nullptr;
+    uint32_t n_blas_launch = 0;
     {   // 4-wide records for the state machine's fast order, cached on (bvh, blas) addresses + upload generations
       uint64_t bvh_bytes = 0, bvh_gen = 0, blas_bytes = 0, blas_gen = 0;
       const uint8_t *nodes = nullptr, *blas_raw = nullptr;
       resolve(a.bvh_addr, sizeof(BvhNodeA), 16, "bvh", &nodes, &bvh_bytes, &bvh_gen);
       resolve(a.blas_addr, sizeof(BlasNodeA), 8, "blas", &blas_raw, &blas_bytes, &blas_gen);
       const uint64_t n_nodes = bvh_bytes / sizeof(BvhNodeA), n_blas = blas_bytes / sizeof(BlasNodeA);
+      n_blas_launch = (uint32_t)std::min<uint64_t>(n_blas, 0xFFFFFFFFu);
       const bool machine = dcr_get(VX_DCR_B200_RT_KERNEL) != 1 && n_nodes < kMachineMaxNodes && n_slots < kMachineMaxNodes;
       const bool want = machine && dcr_get(VX_DCR_B200_RT_ORDER) == 0 && n_nodes > 0 && n_blas > 0;
       if (want) {
@@ -808,6 +810,7 @@ private:
       p.scene = sc, p.arg = a, p.out = out, p.part = part_;
       p.mode = dcr_get(VX_DCR_B200_RT_MODE), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
       p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
+      p.n_blas = n_blas_launch;
       p.quorum_refill = (uint32_t)env_u64("VORTEX_B200_QUORUM_REFILL", 12);
       p.quorum_inner = (uint32_t)env_u64("VORTEX_B200_QUORUM_INNER", 8);
       p.chunk = (uint32_t)env_u64("VORTEX_B200_CHUNK", 32);
@@ -838,6 +841,7 @@ private:
         p.scene = sc, p.arg = a, p.out = nullptr, p.part = Partition{};
         p.mode = 0, p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
         p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
+        p.n_blas = n_blas_launch;
         p.quorum_refill = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_REFILL", 16);
         p.quorum_inner = (uint32_t)env_u64("VORTEX_B200_TRACE_QUORUM_INNER", 12);
         p.chunk = (uint32_t)env_u64("VORTEX_B200_TRACE_CHUNK", 64);   // sweep: profiles/r01_sweep_trace_quorum_chunk.txt
