@@ -82,14 +82,16 @@ _HOST_SCENES = {}
 
 
 def host_scene(wl):
-    """the product's own host builders (reference byte layouts), one build per geometry"""
+    """the product's own host builders (reference byte layouts).  The procedural mesh is generated once per geometry; the scene
+    (BVH2 + TLAS) is rebuilt for every workload because Tracer::setup rotates the instances in place (raycast/tracer.cpp:157-158),
+    so a scene that was set up twice would show a different view."""
     key = (wl["n"], wl.get("scale", 1.0))
     if key not in _HOST_SCENES:
-        t0 = time.perf_counter()
-        hs = pkg("host").HostScene(make_meshes(wl))
-        _HOST_SCENES.clear()            # one 10 M-triangle scene is 1.6 GB of host arrays: keep only the latest
-        _HOST_SCENES[key] = (hs, time.perf_counter() - t0)
-    return _HOST_SCENES[key]
+        _HOST_SCENES.clear()            # one 10 M-triangle mesh is 1 GB of host arrays: keep only the latest
+        _HOST_SCENES[key] = make_meshes(wl)
+    t0 = time.perf_counter()
+    hs = pkg("host").HostScene(_HOST_SCENES[key])
+    return hs, time.perf_counter() - t0
 
 
 def peaks():

@@ -434,3 +434,38 @@ def test_deep_tree_overflow_is_reported_not_silent():
                 tr.run()
     finally:
         tr.close()
+
+
+def test_readback_strips_deliver_the_same_frame():
+    """vx_b200_set_readback: the frame is in page-locked host memory when vx_ready_wait returns.  At benchmark sizes the frame is
+    cut into strips (two kernel streams + a copy stream); any strip count must give the image of the plain call sequence."""
+    import torch
+    port = po.PortRaycast() if po.have_port() else best_oracle()
+    sc = port.scene_create([scenes.heightfield(224)])
+    w, h = 2048, 1100                                   # ragged last band (1100 = 137 bands + 4 rows)
+    karg = sc.setup(w, h)
+    tr = tracer_for(sc, karg)
+    os.environ["VORTEX_B200_SCHEDULE"] = "0"          # row-major tile order on every frame (an ordered schedule runs as one launch)
+    try:
+        for mode in (1, 0):
+            tr.set_mode(mode, 0)
+            want = tr.run().copy()
+            host = torch.zeros((h, w), dtype=torch.int32).pin_memory()
+            tr.dev.set_readback(tr.out, host.data_ptr(), w * h * 4)
+            for strips in ("4", "1", "7", "3"):
+                os.environ["VORTEX_B200_READBACK_STRIPS"] = strips
+                for frame in range(6):                  # frames 0-2 run the schedule trial (no strips), later ones the strips
+                    host.zero_()
+                    tr.dev.start(tr.krnl, tr.args)
+                    tr.dev.ready_wait()
+                    assert np.array_equal(host.numpy().view(np.uint32), want), (mode, strips, frame)
+                    got = np.zeros((h, w), np.uint32)
+                    tr.out.copy_from_dev(got)           # the device framebuffer is complete as well
+                    assert np.array_equal(got, want)
+                    st = tr.dev.stats()
+                    assert st["kernel_launches"] - st["prep_launches"] == int(strips), (strips, st)   # the strips did run
+            tr.dev.set_readback(tr.out, None, 0)
+    finally:
+        os.environ.pop("VORTEX_B200_READBACK_STRIPS", None)
+        os.environ.pop("VORTEX_B200_SCHEDULE", None)
+        tr.close()

@@ -601,6 +601,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
   const uint32_t nbands = nbands_total > f.rank ? (nbands_total - f.rank + f.world - 1) / f.world : 0;
   f.tiles_per_band = (f.band_rows / kTileH) * f.tcols;
   f.total = nbands * f.tiles_per_band * 32u;
+  if (MODE != kModeTrace && p.tile_end) f.total = (min(p.tile_end, nbands * f.tiles_per_band) - p.tile_first) * 32u;   // one strip
   if (MODE == kModeTrace) f.total = (uint32_t)((p.count + 31u) / 32u * 32u);
 
   Lane L;
@@ -681,7 +682,7 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
           }
         } else {
         uint32_t grp, in_tile = item & 31u;
-        uint32_t tile = sched_tile(p.sched, item >> 5, f.total >> 5, grp);
+        uint32_t tile = sched_tile(p.sched, (item >> 5) + p.tile_first, f.total >> 5, grp);   // strips run without a schedule order
         uint32_t band_local = tile / f.tiles_per_band, r = tile % f.tiles_per_band;
         uint32_t trow = r / f.tcols, tcol = r % f.tcols;
         uint32_t x = tcol * kTileW + (in_tile & (kTileW - 1));

@@ -118,6 +118,7 @@ public:
     if (rtu_tri_) cudaFree(rtu_tri_);
     pipe_free_locked();
     alt_free_locked();
+    strips_free_locked();
     ray_order_free_locked();
     sched_free_locked();
     if (counters_) cudaFree(counters_);
@@ -551,6 +552,42 @@ public:
     std::lock_guard<std::mutex> g(mu_);
     peer_fb_arena_ = owner_arena;
   }
+  // Asynchronous readback (vx_b200_set_readback): frames whose framebuffer is `fb_addr` are followed by the copy of this
+  // GPU's bands into page-locked host memory at `host` (the image's first byte).  When the frame runs in row-major tile order
+  // with the ray state machine, it is cut into kStrips strips launched alternately on two streams, and the bands of a finished
+  // strip are copied (copy stream) while the next strips are traced.
+  void set_readback_target(uint64_t fb_addr, uint8_t *host, uint64_t bytes) {
+    std::lock_guard<std::mutex> g(mu_);
+    rb_addr_ = fb_addr, rb_host_ = host, rb_bytes_ = bytes;
+  }
+  bool readback_issued() {
+    std::lock_guard<std::mutex> g(mu_);
+    return rb_issued_;
+  }
+  // bands [b0, b1) of this GPU's own bands (indices into ITS band list) of a W x H image at arena offset `fb`: one strided copy
+  int copy_bands(uint8_t *base, uint64_t fb, uint32_t W, uint32_t H, uint32_t b0, uint32_t b1, cudaStream_t st) {
+    const Partition &p = part_;
+    const uint64_t row = (uint64_t)W * 4, band = row * p.band_rows, pitch = band * p.world;
+    const uint32_t bands_total = (H + p.band_rows - 1) / p.band_rows;
+    const uint32_t mine = bands_total > p.rank ? (bands_total - p.rank + p.world - 1) / p.world : 0;
+    if (b1 > mine) b1 = mine;
+    if (b0 >= b1) return 0;
+    const uint8_t *src = arena_ + fb;
+    // the last band of the image may be short; it belongs to this GPU iff (bands_total - 1) % world == rank
+    const bool short_last = (H % p.band_rows) != 0 && (bands_total - 1) % p.world == p.rank && b1 == mine;
+    const uint32_t full = (b1 - b0) - (short_last ? 1u : 0u);
+    const uint64_t o = band * ((uint64_t)p.rank + (uint64_t)b0 * p.world);
+    if (full == 1 || (p.world == 1 && full)) {
+      CUDA_TRY(cudaMemcpyAsync(base + o, src + o, band * (p.world == 1 ? full : 1), cudaMemcpyDefault, st));
+    } else if (full) {
+      CUDA_TRY(cudaMemcpy2DAsync(base + o, pitch, src + o, pitch, band, full, cudaMemcpyDefault, st));
+    }
+    if (short_last) {
+      const uint64_t lo = band * (uint64_t)(bands_total - 1);
+      CUDA_TRY(cudaMemcpyAsync(base + lo, src + lo, row * (H % p.band_rows), cudaMemcpyDefault, st));
+    }
+    return 0;
+  }
   cudaEvent_t end_event() const { return ev_end_; }
   bool run_pending() {
     std::lock_guard<std::mutex> g(mu_);
@@ -642,6 +679,7 @@ private:
     CUDA_TRY(cudaMemsetAsync(counters_, 0, sizeof(WorkCounters), stream_));
     CUDA_TRY(cudaMemsetAsync(tile_counter_, 0, sizeof(uint32_t), stream_));
     launches_ = 0, prep_launches_ = 0;
+    rb_issued_ = false, kend_valid_ = false;
     CUDA_TRY(cudaEventRecord(ev_begin_, stream_));
     return 0;
   }
@@ -662,7 +700,8 @@ private:
     CUDA_TRY(cudaStreamSynchronize(stream_));
     run_pending_ = false;
     float ms_total = 0, ms_prep = 0;
-    CUDA_TRY(cudaEventElapsedTime(&ms_total, ev_begin_, ev_end_));
+    CUDA_TRY(cudaEventElapsedTime(&ms_total, ev_begin_, kend_valid_ ? ev_kend_ : ev_end_));
+    kend_valid_ = false;
     CUDA_TRY(cudaEventElapsedTime(&ms_prep, ev_begin_, ev_prep_));
     stats_.rays = h_counters_->rays;
     stats_.box_tests = h_counters_->box_tests;
@@ -823,8 +862,53 @@ private:
       bool simple = dcr_get(VX_DCR_B200_RT_KERNEL) == 1 || bvh_bytes / sizeof(BvhNodeA) >= kMachineMaxNodes || n_slots >= kMachineMaxNodes ||
                     (dcr_get(VX_DCR_B200_RT_ORDER) == 0 && !sc.wide);
       // the prep-time event is already recorded: the schedule's small copies count as kernel time
-      if (sched_prepare_locked(0, a.dst_width, a.dst_height, !simple && p.chunk == 32, &p.sched) != 0) return -1;
-      rc = simple ? launch_render_a(p, prop_.multiProcessorCount, stream_) : launch_render_machine(p, prop_.multiProcessorCount, stream_);
+      const bool rb = rb_host_ && rb_addr_ == a.dst_addr && rb_bytes_ >= (uint64_t)a.dst_width * a.dst_height * 4 && !remote_fb_ && !peer_fb_arena_;
+      const uint32_t tiles_per_band = (part_.band_rows / 4) * ((a.dst_width + 7) / 8), ntiles = rank_tiles(a.dst_width, a.dst_height);
+      const uint32_t my_bands = tiles_per_band ? ntiles / tiles_per_band : 0;
+      const uint32_t strips = (uint32_t)env_u64("VORTEX_B200_READBACK_STRIPS", kStrips);
+      // A frame that is read back in strips keeps the row-major tile order (a strip must be a set of whole bands): hiding the
+      // framebuffer copy under the tracing is worth more than the ordered schedule's shorter tail.
+      const bool strip_ok = rb && !simple && strips > 1 && my_bands >= 4 * strips && ntiles >= 16384;
+      if (sched_prepare_locked(0, a.dst_width, a.dst_height, !simple && p.chunk == 32 && !strip_ok, &p.sched) != 0) return -1;
+      if (strip_ok && !p.sched.order) {
+        if (strips_init_locked() != 0) return -1;
+        CUDA_TRY(cudaStreamWaitEvent(aux_stream_, ev_prep_, 0));   // scene records (re)built above, counters zeroed
+        CUDA_TRY(cudaMemsetAsync(strip_counters_, 0, sizeof(uint32_t) * kMaxStrips, stream_));
+        CUDA_TRY(cudaEventRecord(ev_strip_[kMaxStrips], stream_));
+        CUDA_TRY(cudaStreamWaitEvent(aux_stream_, ev_strip_[kMaxStrips], 0));
+        rc = 0;
+        const uint32_t S = std::min<uint32_t>(strips, kMaxStrips);
+        for (uint32_t k = 0; k < S && rc >= 0; k++) {
+          const uint32_t b0 = (uint32_t)((uint64_t)my_bands * k / S), b1 = (uint32_t)((uint64_t)my_bands * (k + 1) / S);
+          cudaStream_t st = (k & 1) ? aux_stream_ : stream_;
+          RenderA q = p;
+          q.tile_first = b0 * tiles_per_band, q.tile_end = b1 * tiles_per_band, q.tile_counter = strip_counters_ + k;
+          q.blocks_per_sm_cap = 0;
+          int r = launch_render_machine(q, prop_.multiProcessorCount, st);
+          if (r < 0) { rc = r; break; }
+          rc += r;
+          CUDA_TRY(cudaEventRecord(ev_strip_[k], st));
+          CUDA_TRY(cudaStreamWaitEvent(copy_stream_, ev_strip_[k], 0));
+          if (copy_bands(rb_host_, a.dst_addr, a.dst_width, a.dst_height, b0, k + 1 == S ? my_bands + 1 : b1, copy_stream_) != 0) return -1;
+        }
+        if (rc >= 0) {   // the main stream joins the other two: kernel time ends where the last strip ends, the run where the last copy ends
+          for (uint32_t k = 0; k < S; k++) CUDA_TRY(cudaStreamWaitEvent(stream_, ev_strip_[k], 0));
+          CUDA_TRY(cudaEventRecord(ev_kend_, stream_));
+          kend_valid_ = true;
+          CUDA_TRY(cudaEventRecord(ev_strip_[kMaxStrips], copy_stream_));
+          CUDA_TRY(cudaStreamWaitEvent(stream_, ev_strip_[kMaxStrips], 0));
+          rb_issued_ = true;
+        }
+      } else {
+        rc = simple ? launch_render_a(p, prop_.multiProcessorCount, stream_) : launch_render_machine(p, prop_.multiProcessorCount, stream_);
+        if (rc >= 0 && rb) {   // one launch: the bands follow it on the same stream
+          if (strips_init_locked() != 0) return -1;
+          CUDA_TRY(cudaEventRecord(ev_kend_, stream_));
+          kend_valid_ = true;
+          if (copy_bands(rb_host_, a.dst_addr, a.dst_width, a.dst_height, 0, my_bands + 1, stream_) != 0) return -1;
+          rb_issued_ = true;
+        }
+      }
     } else {
       uint64_t bvh_bytes = 0;
       const uint8_t *dummy = nullptr;
@@ -1235,6 +1319,31 @@ private:
   uint32_t *remote_fb_ = nullptr;
   uint64_t remote_bytes_ = 0;
   uint8_t *peer_fb_arena_ = nullptr;   // same-process owner of the image (DeviceGroup, VORTEX_B200_FB=peer)
+  // strip-pipelined readback
+  static constexpr uint32_t kStrips = 4, kMaxStrips = 8;
+  uint64_t rb_addr_ = 0, rb_bytes_ = 0;
+  uint8_t *rb_host_ = nullptr;
+  bool rb_issued_ = false, kend_valid_ = false;
+  cudaStream_t aux_stream_ = nullptr, copy_stream_ = nullptr;
+  cudaEvent_t ev_strip_[kMaxStrips + 1] = {}, ev_kend_ = nullptr;
+  uint32_t *strip_counters_ = nullptr;
+  int strips_init_locked() {
+    if (aux_stream_) return 0;
+    CUDA_TRY(cudaStreamCreateWithFlags(&aux_stream_, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    for (auto &e : ev_strip_) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreate(&ev_kend_));
+    CUDA_TRY(cudaMalloc(&strip_counters_, sizeof(uint32_t) * kMaxStrips));
+    return 0;
+  }
+  void strips_free_locked() {
+    if (!aux_stream_) return;
+    cudaStreamDestroy(aux_stream_), cudaStreamDestroy(copy_stream_);
+    for (auto &e : ev_strip_) cudaEventDestroy(e), e = nullptr;
+    cudaEventDestroy(ev_kend_);
+    cudaFree(strip_counters_);
+    aux_stream_ = copy_stream_ = nullptr, ev_kend_ = nullptr, strip_counters_ = nullptr;
+  }
   uint8_t *stage_ = nullptr;           // page-locked ring for small uploads
   cudaEvent_t stage_ev_[kStageSlots] = {};
   int stage_next_ = 0;
