@@ -614,6 +614,73 @@ def measure_incoherent(name, gpus, steps, warmup, cpu=False, clocks=False):
             "host_bvh_build_s": round(build_s, 3)}
 
 
+def measure_dynamic_scene(gpus, steps, name="primary_4k_1m"):
+    """SURVEY 8f-1 in use: a scene whose triangles change every frame.  Per frame, end to end with HOST buffers: upload the triangle
+    and attribute buffers, build the BVH2 ON THE GPU into the reference's own node / index buffers (vx_b200_build_bvh), render,
+    download the image — against the same frame with the host's binned-SAH builder (the reference's algorithm, task-parallel)
+    followed by the upload of all seven buffers.  The GPU-built tree is checked with the CPU checker on the downloaded bytes."""
+    import torch
+
+    tracer_mod = pkg("tracer")
+    wl = WORKLOADS[name]
+    W, H = wl["w"], wl["h"]
+    hs, host_build_s = host_scene(wl)
+    karg = hs.setup(W, H, spp=1, max_depth=wl["depth"])
+    bufs = hs.buffers()
+    ntri = bufs["tri"].nbytes // 36
+    tr = tracer_mod.Tracer(W, H, 1, wl["depth"], cuda_device=0, gpus=gpus).init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names})
+    tr.set_mode(wl["mode"], 0)
+    tr._upload_args()
+    dev = tr.dev
+    pinned = {n: torch.from_numpy(bufs[n].copy()).pin_memory() for n in tracer_mod.SCENE_BUFFERS if bufs[n].nbytes}
+    out_pinned = torch.empty((H, W), dtype=torch.int32).pin_memory()
+
+    def frame(gpu_build):
+        for n in (("tri", "triEx") if gpu_build else pinned):
+            tr.bufs[n].copy_to_dev((pinned[n].data_ptr(), pinned[n].numel()))
+        if gpu_build:
+            dev.build_bvh(tr.bufs["tri"], ntri, tr.bufs["bvh"], tr.bufs["triIdx"])
+        tr._upload_args()
+        dev.start(tr.krnl, tr.args)
+        dev.ready_wait()
+        tr.out.copy_from_dev((out_pinned.data_ptr(), W * H * 4))
+
+    def timed(gpu_build, n):
+        for _ in range(4):
+            frame(gpu_build)
+        t0 = time.perf_counter()
+        for _ in range(n):
+            frame(gpu_build)
+        return (time.perf_counter() - t0) / n * 1e3, dev.stats()["kernel_ms"]
+
+    host_ms, host_kernel_ms = timed(False, steps)
+    frame_host_tree = out_pinned.numpy().view(np.uint32).copy()
+    gpu_ms, gpu_kernel_ms = timed(True, steps)
+    dev.build_bvh(tr.bufs["tri"], ntri, tr.bufs["bvh"], tr.bufs["triIdx"])
+    build_ms = dev.stats()["kernel_ms"]
+    frame(True)
+    frame_gpu_tree = out_pinned.numpy().view(np.uint32).copy()
+    # the reference's traversal on the GPU-built tree (downloaded bytes)
+    gb = dict(bufs)
+    for n in ("bvh", "triIdx"):
+        a = np.zeros(bufs[n].nbytes, np.uint8)
+        tr.bufs[n].copy_from_dev(a)
+        gb[n] = a
+    par = parity_frames(tr, wl, gb, karg, frame_gpu_tree, gpus, order="fast, GPU-built tree")
+    par["pixels_differ_from_host_tree_frame"] = int((frame_gpu_tree != frame_host_tree).sum())
+    rays = dev.stats()["rays"]
+    tr.close()
+    return {"workload": name + " with the triangles re-uploaded and the BVH rebuilt every frame", "triangles": ntri, "n_gpus": gpus, "steps": steps,
+            "gpu_build": {"e2e_ms_per_frame": gpu_ms, "e2e_mrays_per_s": rays / gpu_ms / 1e3, "build_ms": build_ms, "render_kernel_ms": gpu_kernel_ms,
+                          "sequence": "vx_copy_to_dev(tri, triEx) + vx_b200_build_bvh + vx_upload_bytes(args) + vx_start + vx_ready_wait + vx_copy_from_dev"},
+            "host_build": {"e2e_ms_per_frame_excluding_build": host_ms, "host_build_ms": host_build_s * 1e3,
+                           "e2e_ms_per_frame": host_ms + host_build_s * 1e3, "render_kernel_ms": host_kernel_ms,
+                           "builder": "vortex-raytracing_b200/host (binned SAH, byte-identical to the reference's builder, all host threads)"},
+            "tree_quality": {"render_kernel_ms_gpu_tree_over_host_tree": gpu_kernel_ms / host_kernel_ms},
+            "speedup_per_frame": (host_ms + host_build_s * 1e3) / gpu_ms, "parity": par}
+
+
 def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
     """layout B (simx RT-unit path, quantized BVH4): kernel-only Mrays/s of k_rtu_render on the cfg1 geometry, its algorithmic
     bytes (52 B per node read + 52 B per instance entered + 36 B per triangle tested + 156 B per shaded hit + 4 B per
@@ -737,6 +804,7 @@ def run_b200(args, name):
                 secondary[other] = measure_frames(other, args.gpus, sec_steps, args.warmup, kernel=args.kernel)
         if args.gpus >= 8 and not incoherent:
             secondary["cfg4_incoherent_10m"] = measure_incoherent("cfg4_incoherent_10m", args.gpus, sec_steps, args.warmup)
+        secondary["dynamic_scene_4k_1m"] = measure_dynamic_scene(args.gpus, sec_steps)
         secondary["rtu_1080p_primary_100k"] = quick_run_rtu(steps=sec_steps, with_cpu=not args.no_cpu)
     multi = ("one vx_device_h over %d GPUs in one process (vx_b200_select_gpus): uploads sliced over %d PCIe links and replicated over "
              "NVLink (%s), %d-row bands round-robin, band-wise download (%s)" %

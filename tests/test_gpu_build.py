@@ -13,14 +13,20 @@ po = pyoracle()
 BVH_DT = np.dtype([("lo", "<f4", 3), ("leftFirst", "<u4"), ("hi", "<f4", 3), ("triCount", "<u4")])
 
 
-def gpu_built_scene(oracle, mesh, w, h):
+def gpu_built_scene(oracle, mesh, w, h, leaf_max=None):
     sc = oracle.scene_create([mesh])
     karg = sc.setup(w, h)
     bufs = sc.buffers()
     n = mesh["tris"].shape[0]
     tr = tracer_mod.Tracer(w, h, 1, 1).init(bufs)
     tr.setup({k: karg[k][0] for k in karg.dtype.names})
-    used = tr.dev.build_bvh(tr.bufs["tri"], n, tr.bufs["bvh"], tr.bufs["triIdx"])
+    import os
+    if leaf_max is not None:
+        os.environ["VORTEX_B200_BUILD_MAX_LEAF"] = str(leaf_max)
+    try:
+        used = tr.dev.build_bvh(tr.bufs["tri"], n, tr.bufs["bvh"], tr.bufs["triIdx"])
+    finally:
+        os.environ.pop("VORTEX_B200_BUILD_MAX_LEAF", None)
     assert used == 2 * n - 1
     st = tr.dev.stats()
     bvh = np.zeros(len(bufs["bvh"]), np.uint8)
@@ -38,24 +44,43 @@ def gpu_built_scene(oracle, mesh, w, h):
 
 @pytest.mark.parametrize("name,mk", [("cornell", lambda: scenes.cornell_box()), ("hf64", lambda: scenes.heightfield(64)),
                                      ("ico3", lambda: scenes.icosphere((0, 0, 0), 1.0, 3))], ids=["cornell", "hf64", "ico3"])
-def test_gpu_built_bvh(name, mk):
+@pytest.mark.parametrize("leaf_max", [4, 1, 14], ids=["leaf4_default", "leaf1", "leaf14"])
+def test_gpu_built_bvh(name, mk, leaf_max):
     oracle = best_oracle()
     mesh = mk()
     n = mesh["tris"].shape[0]
-    sc, karg, bufs, gb, tr, st = gpu_built_scene(oracle, mesh, 96, 72)
+    sc, karg, bufs, gb, tr, st = gpu_built_scene(oracle, mesh, 96, 72, leaf_max)
     try:
         nodes = gb["bvh"].view(BVH_DT)[: 2 * n - 1]
         idx = gb["triIdx"].view(np.uint32)
         assert sorted(idx.tolist()) == list(range(n))
-        leaves = nodes[nodes["triCount"] != 0]
-        assert len(leaves) == n and (leaves["triCount"] == 1).all() and sorted(leaves["leftFirst"].tolist()) == list(range(n))
-        inner = np.flatnonzero(nodes["triCount"] == 0)
-        assert len(inner) == n - 1
-        # boxes: a parent's box is the union of its two (adjacent) children; a leaf's box is its triangle's vertex min/max
+        # the tree reachable from the root (nodes below a subtree that was priced into one leaf stay behind as fillers)
+        reach, todo = [], [0]
+        while todo:
+            k = todo.pop()
+            reach.append(k)
+            if nodes["triCount"][k] == 0:
+                todo += [int(nodes["leftFirst"][k]), int(nodes["leftFirst"][k]) + 1]
+        reach = np.array(sorted(reach))
+        assert len(set(reach.tolist())) == len(reach)                       # every node referenced once
+        rn = nodes[reach]
+        leaves = rn[rn["triCount"] != 0]
+        slots = np.concatenate([np.arange(f, f + c) for f, c in zip(leaves["leftFirst"], leaves["triCount"])])
+        assert sorted(slots.tolist()) == list(range(n))                     # every triangle in exactly one leaf
+        assert leaves["triCount"].max() <= leaf_max
+        inner = reach[nodes["triCount"][reach] == 0]
+        assert len(inner) == len(leaves) - 1
+        # boxes: a parent's box is the union of its two (adjacent) children; a leaf's box is its triangles' vertex min/max
         l, r = nodes[nodes["leftFirst"][inner]], nodes[nodes["leftFirst"][inner] + 1]
         assert np.array_equal(nodes["lo"][inner], np.minimum(l["lo"], r["lo"])) and np.array_equal(nodes["hi"][inner], np.maximum(l["hi"], r["hi"]))
-        tri = bufs["tri"].view(np.float32).reshape(-1, 3, 3)[idx[leaves["leftFirst"]]]
-        assert np.array_equal(leaves["lo"], tri.min(axis=1)) and np.array_equal(leaves["hi"], tri.max(axis=1))
+        tri = bufs["tri"].view(np.float32).reshape(-1, 3, 3)
+        for lf in leaves[:: max(1, len(leaves) // 500)]:
+            v = tri[idx[lf["leftFirst"]: lf["leftFirst"] + lf["triCount"]]].reshape(-1, 3)
+            assert np.array_equal(lf["lo"], v.min(axis=0)) and np.array_equal(lf["hi"], v.max(axis=0))
+        if leaf_max == 1:
+            assert len(leaves) == n
+        elif name == "hf64":
+            assert len(leaves) < 0.75 * n                                   # the two triangles of a quad share a box: one leaf
         # the reference's traversal on the GPU-built tree vs on the host-built tree
         raw = po.RawScene(oracle, gb, karg)
         h_gpu_tree = raw.trace_primary(threads=oracle.hw_threads())

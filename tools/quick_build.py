@@ -35,12 +35,18 @@ def frame_ms():
 
 host_ms = frame_ms()
 nt = mesh["tris"].shape[0]
-tr.dev.build_bvh(tr.bufs["tri"], nt, tr.bufs["bvh"], tr.bufs["triIdx"])
-tr.dev.build_bvh(tr.bufs["tri"], nt, tr.bufs["bvh"], tr.bufs["triIdx"])
-gpu_build_ms = tr.dev.stats()["kernel_ms"]
-gpu_ms = frame_ms()
-print(f"triangles={nt} host_build_s={host_s:.3f} gpu_build_ms={gpu_build_ms:.2f} primary_4k_frame_ms host_tree={host_ms:.3f} gpu_tree={gpu_ms:.3f}")
+print(f"triangles={nt} host_build_s={host_s:.3f} primary_4k_frame_ms host SAH tree={host_ms:.3f}")
+for leaf, ctrav in ((1, 1.0), (2, 0.0), (2, 1.0), (4, 0.0), (4, 0.5), (4, 1.0), (4, 2.0), (8, 1.0), (8, 2.0), (14, 2.0)):
+    os.environ["VORTEX_B200_BUILD_MAX_LEAF"], os.environ["VORTEX_B200_BUILD_CTRAV"] = str(leaf), str(ctrav)
+    tr.dev.build_bvh(tr.bufs["tri"], nt, tr.bufs["bvh"], tr.bufs["triIdx"])
+    tr.dev.build_bvh(tr.bufs["tri"], nt, tr.bufs["bvh"], tr.bufs["triIdx"])
+    gpu_build_ms = tr.dev.stats()["kernel_ms"]
+    gpu_ms = frame_ms()
+    print(f"  GPU build max_leaf={leaf} c_trav={ctrav}: build {gpu_build_ms:.2f} ms, frame {gpu_ms:.3f} ms = {gpu_ms / host_ms:.3f} x the SAH tree's")
+os.environ.pop("VORTEX_B200_BUILD_MAX_LEAF"), os.environ.pop("VORTEX_B200_BUILD_CTRAV")
 tr.close()
+if os.environ.get("LAYOUT_A_ONLY"):
+    sys.exit(0)
 
 # ---- layout B: quantized BVH4 (vx_b200_build_qbvh) ----
 rtx = importlib.import_module("vortex-raytracing_b200.rtx_tracer")

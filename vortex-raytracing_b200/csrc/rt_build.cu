@@ -12,7 +12,13 @@
 // Algorithm: linear BVH — 63-bit Morton codes of the triangle centroids (21 bits per axis, duplicates disambiguated by
 // index), one CUB radix sort, Karras' parallel radix-tree construction (one thread per internal node), bottom-up box fit
 // with one atomic counter per internal node, then a relabelling pass that lays the children of internal node i at slots
-// 1+2i and 2+2i so the reference's "children are adjacent" addressing holds.  One-triangle leaves.
+// 1+2i and 2+2i so the reference's "children are adjacent" addressing holds.
+// Leaves (layout A): the bottom-up pass that fits the boxes also prices every subtree with the surface-area heuristic —
+// cost(node) = min(n * A * C_tri, C_trav * A + cost(left) + cost(right)), the criterion of the reference's subdivide()
+// (raycast/bvh.cpp:40-48: split only if the children cost less than the unsplit node) with a traversal term — and a subtree of
+// at most max_leaf triangles whose leaf cost is the smaller one becomes ONE leaf (its triangles are a contiguous range of the
+// Morton order, i.e. of triIdx, exactly the reference's leaf format).  The two triangles of a quad share their box, so they
+// end up in one leaf as in the reference's trees; nodes below a collapsed node stay in the buffer as unreachable fillers.
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cfloat>
@@ -89,10 +95,14 @@ __global__ void k_morton(const float *__restrict__ tri, uint32_t n, const float 
   if (i >= n) return;
   const float *t = tri + (size_t)i * 9;
   uint32_t q[3];
+  // one grid step for all three axes (the largest extent): a thin axis — the height of a terrain — then only differs in its low
+  // bits, so the radix tree does not cut along it before the other two axes have been cut to the same scale.  Normalising every
+  // axis by its own extent made every third split a useless one across the terrain's thickness (measured: 4K frame 1.52x the
+  // SAH tree's time before, profiles/r02_sweep_gpu_build.txt)
+  const float ext = fmaxf(fmaxf(cb[3] - cb[0], cb[4] - cb[1]), cb[5] - cb[2]);
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     float c = (t[a] + t[3 + a] + t[6 + a]) * (1.0f / 3.0f);
-    float ext = cb[3 + a] - cb[a];
     float u = ext > 0 ? (c - cb[a]) / ext : 0.0f;
     u = fminf(fmaxf(u, 0.0f), 1.0f);
     q[a] = min((uint32_t)(u * 2097151.0f), 2097151u);
@@ -141,9 +151,24 @@ __global__ void k_radix_tree(const uint64_t *__restrict__ keys, int n, uint2 *__
 }
 
 // bottom-up: the second thread to reach an internal node merges its children's boxes and climbs on
+constexpr uint32_t kCollapsed = 0x80000000u;   // flag in SahInfo::count: this internal node is emitted as one leaf
+struct SahInfo {                                // per internal node, written by the thread that fits its box
+  uint32_t count;                               // triangles below (| kCollapsed)
+  uint32_t first;                               // their first position in Morton order
+  float cost;                                   // SAH cost of the subtree as it will be emitted
+};
+struct SahParams {
+  float c_trav, c_tri;
+  uint32_t max_leaf;                            // 1 = one-triangle leaves (no pricing)
+};
+__device__ __forceinline__ float half_area(float lx, float ly, float lz, float hx, float hy, float hz) {
+  const float ex = hx - lx, ey = hy - ly, ez = hz - lz;
+  return ex * ey + ey * ez + ez * ex;
+}
+
 __global__ void k_fit(const uint2 *__restrict__ children, const uint32_t *__restrict__ parent_int, const uint32_t *__restrict__ parent_leaf,
                       const uint32_t *__restrict__ vals, const Box3 *__restrict__ leaf_box, Box3 *__restrict__ int_box,
-                      uint32_t *__restrict__ arrived, uint32_t n) {
+                      uint32_t *__restrict__ arrived, uint32_t n, SahInfo *__restrict__ sah, SahParams sp) {
   uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
   if (l >= n) return;
   uint32_t cur = parent_leaf[l];
@@ -159,6 +184,20 @@ __global__ void k_fit(const uint2 *__restrict__ children, const uint32_t *__rest
       m.lo[k] = fminf(a->lo[k], b->lo[k]);
       m.hi[k] = fmaxf(a->hi[k], b->hi[k]);
     }
+    if (sah) {
+      const volatile SahInfo *sa = (c.x & kLeafBit) ? nullptr : &sah[c.x], *sb = (c.y & kLeafBit) ? nullptr : &sah[c.y];
+      const uint32_t na = sa ? (sa->count & ~kCollapsed) : 1u, nb = sb ? (sb->count & ~kCollapsed) : 1u;
+      const uint32_t fa = sa ? sa->first : (c.x & ~kLeafBit), fb = sb ? sb->first : (c.y & ~kLeafBit);
+      const float ca = sa ? sa->cost : sp.c_tri * half_area(a->lo[0], a->lo[1], a->lo[2], a->hi[0], a->hi[1], a->hi[2]);
+      const float cb = sb ? sb->cost : sp.c_tri * half_area(b->lo[0], b->lo[1], b->lo[2], b->hi[0], b->hi[1], b->hi[2]);
+      const float A = half_area(m.lo[0], m.lo[1], m.lo[2], m.hi[0], m.hi[1], m.hi[2]);
+      const uint32_t nn = na + nb;
+      const float leaf_cost = sp.c_tri * (float)nn * A, split_cost = sp.c_trav * A + ca + cb;
+      const bool col = nn <= sp.max_leaf && leaf_cost <= split_cost;
+      sah[cur].count = nn | (col ? kCollapsed : 0u);
+      sah[cur].first = fa < fb ? fa : fb;
+      sah[cur].cost = col ? leaf_cost : split_cost;
+    }
     int_box[cur] = m;
     cur = parent_int[cur];
   }
@@ -173,7 +212,7 @@ __device__ __forceinline__ void write_node(BvhNodeA *out, const Box3 &b, uint32_
 // relabel into the reference layout: root at 0, the children of internal node i at 1+2i and 2+2i
 __global__ void k_emit(const uint2 *__restrict__ children, const uint32_t *__restrict__ vals, const Box3 *__restrict__ leaf_box,
                        const Box3 *__restrict__ int_box, uint32_t n, BvhNodeA *__restrict__ nodes, uint32_t *__restrict__ triIdx,
-                       uint32_t tri_first) {
+                       uint32_t tri_first, const SahInfo *__restrict__ sah, const uint32_t *__restrict__ parent_int) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) triIdx[i] = tri_first + vals[i];
   if (n == 1) {
@@ -181,7 +220,14 @@ __global__ void k_emit(const uint2 *__restrict__ children, const uint32_t *__res
     return;
   }
   if (i >= n - 1) return;
-  if (i == 0) write_node(nodes, int_box[0], 1u, 0u);
+  // below a collapsed node (or being one) this node's children are unreachable: they are written as one-triangle fillers
+  bool below = sah && (sah[i].count & kCollapsed);
+  if (sah)
+    for (uint32_t p = parent_int[i]; !below && p != 0xFFFFFFFFu; p = parent_int[p]) below = (sah[p].count & kCollapsed) != 0;
+  if (i == 0) {
+    if (below) write_node(nodes, int_box[0], sah[0].first, sah[0].count & ~kCollapsed);   // the whole mesh is one leaf
+    else write_node(nodes, int_box[0], 1u, 0u);
+  }
   uint2 c = children[i];
   uint32_t cc[2] = {c.x, c.y};
 #pragma unroll
@@ -190,6 +236,10 @@ __global__ void k_emit(const uint2 *__restrict__ children, const uint32_t *__res
     if (cc[k] & kLeafBit) {
       uint32_t pos = cc[k] & ~kLeafBit;
       write_node(dst, leaf_box[vals[pos]], pos, 1u);          // leaf: triIdx slot `pos` (instance-local), one triangle
+    } else if (below) {
+      write_node(dst, int_box[cc[k]], sah[cc[k]].first, 1u);  // filler (a leaf, so later passes skip it)
+    } else if (sah && (sah[cc[k]].count & kCollapsed)) {
+      write_node(dst, int_box[cc[k]], sah[cc[k]].first, sah[cc[k]].count & ~kCollapsed);   // a priced subtree as one leaf
     } else {
       write_node(dst, int_box[cc[k]], 1u + 2u * cc[k], 0u);   // inner: its own children pair
     }
@@ -209,12 +259,13 @@ struct Lbvh {
   uint64_t *keys = nullptr, *keys2 = nullptr;
   uint32_t *vals = nullptr, *vals2 = nullptr, *parent_int = nullptr, *parent_leaf = nullptr, *arrived = nullptr;
   uint2 *children = nullptr;
+  SahInfo *sah = nullptr;            // layout A with max_leaf > 1
   void *tmp = nullptr;
   const uint32_t *order = nullptr;   // sorted position -> triangle (points into vals / vals2)
   int launches = 0;
   void release() {
     cudaFree(cb), cudaFree(leaf_box), cudaFree(int_box), cudaFree(keys), cudaFree(keys2), cudaFree(vals), cudaFree(vals2);
-    cudaFree(parent_int), cudaFree(parent_leaf), cudaFree(arrived), cudaFree(children), cudaFree(tmp);
+    cudaFree(parent_int), cudaFree(parent_leaf), cudaFree(arrived), cudaFree(children), cudaFree(tmp), cudaFree(sah);
   }
 };
 
@@ -223,7 +274,7 @@ struct Lbvh {
     if (e == cudaSuccess) e = (x);     \
   } while (0)
 
-cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t) {
+cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t, SahParams sp = SahParams{0.f, 1.f, 1u}) {
   size_t tmp_bytes = 0;
   cudaError_t e = cudaSuccess;
   VXB_TRY(alloc(&t.cb, 6));
@@ -237,6 +288,7 @@ cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t)
   VXB_TRY(alloc(&t.parent_leaf, n));
   VXB_TRY(alloc(&t.arrived, n));
   VXB_TRY(alloc(&t.children, n));
+  if (sp.max_leaf > 1) VXB_TRY(alloc(&t.sah, n));
   cub::DoubleBuffer<uint64_t> dk(t.keys, t.keys2);
   cub::DoubleBuffer<uint32_t> dv(t.vals, t.vals2);
   VXB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
@@ -253,7 +305,7 @@ cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t)
   t.order = dv.Current();
   if (n > 1 && e == cudaSuccess) {
     k_radix_tree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(dk.Current(), (int)n, t.children, t.parent_int, t.parent_leaf);
-    k_fit<<<blocks, 256, 0, stream>>>(t.children, t.parent_int, t.parent_leaf, t.order, t.leaf_box, t.int_box, t.arrived, n);
+    k_fit<<<blocks, 256, 0, stream>>>(t.children, t.parent_int, t.parent_leaf, t.order, t.leaf_box, t.int_box, t.arrived, n, t.sah, sp);
     t.launches += 2;
   }
   VXB_TRY(cudaGetLastError());
@@ -390,12 +442,15 @@ __global__ void k_b_root_box(const Box3 *__restrict__ leaf_box, const Box3 *__re
 
 }  // namespace
 
-int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches) {
+int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches,
+               float c_trav, uint32_t max_leaf) {
   if (n == 0) return -(int)cudaErrorInvalidValue;
+  if (max_leaf < 1) max_leaf = 1;
+  if (max_leaf > 14) max_leaf = 14;   // the kernels' leaf cursors carry counts below 15
   Lbvh t;
-  cudaError_t e = lbvh_tree(reinterpret_cast<const float *>(tri), n, stream, t);
+  cudaError_t e = lbvh_tree(reinterpret_cast<const float *>(tri), n, stream, t, SahParams{c_trav, 1.0f, max_leaf});
   if (e == cudaSuccess) {
-    k_emit<<<(n + 255) / 256, 256, 0, stream>>>(t.children, t.order, t.leaf_box, t.int_box, n, nodes, triIdx, tri_first);
+    k_emit<<<(n + 255) / 256, 256, 0, stream>>>(t.children, t.order, t.leaf_box, t.int_box, n, nodes, triIdx, tri_first, t.sah, t.parent_int);
     t.launches += 1;
     VXB_TRY(cudaGetLastError());
     VXB_TRY(cudaStreamSynchronize(stream));

@@ -6,7 +6,10 @@
 namespace vxb {
 // Builds the BVH2 of triangles tri[0..n) into nodes[0..2n-1) and triIdx[0..n) (values tri_first + i, leaf order).
 // Synchronous on `stream`.  Returns 0 or a negative cudaError_t; *launches = kernels launched (the CUB sort counted once).
-int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches);
+// Leaves: subtrees of at most max_leaf triangles become one leaf where the surface-area heuristic prices the leaf no higher than
+// the split (c_trav = cost of one node visit relative to one triangle test); max_leaf = 1 keeps one-triangle leaves.
+int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches,
+               float c_trav = 1.0f, uint32_t max_leaf = 4);
 // Layout B (second half): the same radix tree collapsed to a BVH4 and quantized into the RT unit's 52-byte nodes
 // (raytracing/bvh.cpp:163-258), one-triangle leaves.  tri[0..n) and triEx[0..n) (may be null) are PERMUTED IN PLACE into leaf
 // order, because layout B addresses triangles without an index array; leaf.leftFirst = tri_first + position.  Node indices are

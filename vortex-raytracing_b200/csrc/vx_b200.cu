@@ -439,7 +439,10 @@ public:
     CUDA_TRY(cudaEventCreate(&e0));
     CUDA_TRY(cudaEventCreate(&e1));
     CUDA_TRY(cudaEventRecord(e0, stream_));
-    int rc = build_lbvh(tri, (uint32_t)tri_count, nodes, idx, (uint32_t)tri_first, stream_, &nl);
+    const char *ct = getenv("VORTEX_B200_BUILD_CTRAV");
+    const float c_trav = ct && *ct ? (float)atof(ct) : 1.0f;
+    int rc = build_lbvh(tri, (uint32_t)tri_count, nodes, idx, (uint32_t)tri_first, stream_, &nl, c_trav,
+                        (uint32_t)env_u64("VORTEX_B200_BUILD_MAX_LEAF", 4));
     cudaEventRecord(e1, stream_);
     cudaEventSynchronize(e1);
     float ms = 0;

@@ -1,4 +1,7 @@
-"""Screen-space sharding of one frame over the GPUs of a box, one process per GPU.
+"""Screen-space sharding of one frame over several PROCESSES, one per GPU — the round-1 arrangement, kept for
+hosts that run one Vortex process per GPU.  The backend itself now spans the GPUs of a box behind ONE vx_device_h
+(VORTEX_B200_GPUS / vx_b200_select_gpus, csrc/vx_group.inc), which is what bench.py measures; this module keeps the band
+arithmetic the tests use and the torch.distributed helpers.
 
 The image is cut into bands of `band_rows` rows; band j belongs to rank j % world (the same rule the CUDA tile scheduler
 applies after vx_b200_set_partition).  The scene is replicated: every rank uploads the same buffers through vx_copy_to_dev.
@@ -36,6 +39,27 @@ def rays_per_rank(width, height, world, band_rows=8):
     return [int(len(owned_rows(r, world, height, band_rows))) * width for r in range(world)]
 
 
+class _runtime_stream:
+    """Run the enclosed collectives on the vx runtime's own CUDA stream (vx_b200_stream) and wait for them before returning: the
+    runtime issues all of its work on that non-blocking stream and does not synchronise with torch's current stream, so a
+    collective left on torch's stream could race the next vx_start or a download.  No-op for CPU tensors (gloo tests)."""
+
+    def __init__(self, tensor, stream):
+        self.ctx = None
+        if stream and tensor.is_cuda:
+            self.ext = torch.cuda.ExternalStream(int(stream), device=tensor.device)
+            self.ctx = torch.cuda.stream(self.ext)
+
+    def __enter__(self):
+        if self.ctx:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx:
+            self.ctx.__exit__(*a)
+            self.ext.synchronize()
+
+
 def _padded_view(fb, band_rows, world):
     """fb [H, W] -> (padded [NBpad, band_rows, W] or a view when no padding is needed, NBpad)"""
     H, W = fb.shape
@@ -48,11 +72,18 @@ def _padded_view(fb, band_rows, world):
     return pad.view(nb_pad, band_rows, W), nb_pad, True
 
 
-def gather_framebuffer(fb, rank, world, band_rows=8, group=None, dst=0):
+def gather_framebuffer(fb, rank, world, band_rows=8, group=None, dst=0, stream=None):
     """fb: [H, W] int32/uint32-as-int32 tensor (this rank's framebuffer; only its own bands are valid).
-    On return rank `dst`'s fb holds every band.  One gather of H*W*4/world bytes per non-root rank."""
+    On return rank `dst`'s fb holds every band.  One gather of H*W*4/world bytes per non-root rank.
+    stream: the runtime's CUDA stream (Device.stream()) when fb aliases a vx buffer — the gather then runs on it and has
+    completed when this returns."""
     if world == 1:
         return fb
+    with _runtime_stream(fb, stream):
+        return _gather_framebuffer(fb, rank, world, band_rows, group, dst)
+
+
+def _gather_framebuffer(fb, rank, world, band_rows, group, dst):
     H, W = fb.shape
     bands, nb_pad, padded = _padded_view(fb, band_rows, world)
     mine = bands[rank::world].contiguous()                       # pack my bands: [NBpad/world, band_rows, W]
@@ -108,7 +139,8 @@ def broadcast_scene(tracer, tensors, rank, world, src=0, group=None):
     if world == 1:
         return
     for name, t in tensors.items():
-        dist.broadcast(t, src=src, group=group)
+        with _runtime_stream(t, tracer.dev.stream()):      # on the runtime's stream, complete before mark_written
+            dist.broadcast(t, src=src, group=group)
     if rank != src:
         for name in tensors:
             tracer.bufs[name].mark_written()
