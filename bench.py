@@ -744,6 +744,7 @@ def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
            "shader_program_kernel": {"kernel": "k_rtu_program<ShippedShaders> (fast order)", "kernel_ms": program_ms,
                                      "mrays_per_s": rays / (program_ms * 1e3)},
            "note": "kernel time only (CUDA events), L2 flushed before every frame; algorithmic work = the reference's trail/short-stack order (strict)"}
+    out["incoherent_rays"] = rtu_incoherent()
     if with_cpu:
         R = importlib.import_module("oracle.pyoracle_rtu")
         orc = R.best()
@@ -760,6 +761,62 @@ def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
         out["cpu_rtu_baseline"] = {"value": len(rays_cpu) / best / 1e6, "unit": "Mrays/s", "cores": threads,
                                    "kind": "reference" if orc.name == "ref" else "port",
                                    "sample": f"traversal of the {rows} centre rows of {w}x{h} (sim/simx/rt_traversal.cpp order), best of 2"}
+    return out
+
+
+def rtu_incoherent(n=708, R=1 << 22, steps=10):
+    """layout B, hit records of incoherent rays (BASELINE configs[4]'s shape on the 1 M-triangle scene): vx_b200_trace_rays through
+    the ray state machine of rt_machine_b.cu against the one-ray-per-lane kernel, records checked with the CPU checker (the
+    RT unit's traversal, sim/simx/rt_traversal.cpp order with the TLAS base fixed) on a sample."""
+    host, rtx, scenes = pkg("host"), pkg("rtx_tracer"), pkg("scenes")
+    mesh = scenes.heightfield(n)
+    bmesh = {"tris": mesh["tris"], "triex": mesh["triex"], "texid": np.zeros(mesh["tris"].shape[0], np.uint32),
+             "materials": [{"tex": mesh["tex"]}], "reflectivity": 0.0}
+    hs = host.RtxHostScene([bmesh])
+    karg = hs.setup(8, 8, spp=1, max_depth=1)
+    bufs = hs.buffers()
+    tr = rtx.RtxTracer(8, 8, 1, 1, cuda_device=0).init(bufs)
+    tr.setup({k: karg[k][0] for k in karg.dtype.names}, camera=rtx.CAMERA_PINHOLE)
+    tr._upload_args()
+    rays = scenes.random_rays(R, (-1.0, -0.05, -1.0), (1.0, 0.45, 1.0), seed=1)
+    rb, hb = tr.dev.upload_bytes(rays), tr.dev.mem_alloc(R * 24)
+    res, recs = {}, {}
+    for mach in ("0", "1"):
+        os.environ["VORTEX_B200_RTU_MACHINE"] = mach
+        ms = []
+        for i in range(steps + 3):
+            tr.dev.flush_l2()
+            tr.dev.trace_rays(tr.args, rb, R, hb)
+            tr.dev.ready_wait()
+            if i >= 3:
+                ms.append(tr.dev.last_kernel_ms())
+        a = np.zeros(R * 24, np.uint8)
+        hb.copy_from_dev(a)
+        recs[mach] = a
+        res[mach] = R / float(np.mean(ms)) / 1e3
+    os.environ.pop("VORTEX_B200_RTU_MACHINE", None)
+    out = {"triangles": 2 * n * n, "rays": R, "steps": steps, "mrays_per_s": res["1"], "kernel": "k_rtu_machine<trace> (ray state machine, stack ring)",
+           "one_ray_per_lane_mrays_per_s": res["0"], "identical_records": bool(np.array_equal(recs["0"], recs["1"])),
+           "note": "kernel time only (CUDA events), L2 flushed before every launch"}
+    try:
+        Rm = importlib.import_module("oracle.pyoracle_rtu")
+        port = Rm.RtuPort()
+        img = Rm.Image(bufs, karg)
+        ns = 1 << 16
+        port.set_fix_tlas_base(1)
+        try:
+            ref = port.trace_rays(img, rays[:ns], threads=os.cpu_count() or 1)
+        finally:
+            port.set_fix_tlas_base(0)
+        hp = pkg("parity").hit_parity(np.frombuffer(recs["1"].tobytes(), dtype=pkg("tracer").HIT_DT)[:ns], ref)
+        out["parity"] = {"checker": "port (rt_traversal.cpp restated, TLAS base fixed)", "rays": hp["n"], "id_mismatch": hp["mismatch"], "ties": hp["ties"],
+                         "non_tie": hp["non_tie"], "max_rel_t": hp["max_rel_t"],
+                         "green": bool(hp["non_tie"] == 0 and hp["mismatch_frac"] <= 1e-4 and hp["max_rel_t"] <= 1e-5)}
+    except Exception as ex:   # the checker library did not travel
+        out["parity"] = {"unavailable": str(ex)[:200]}
+    rb.free()
+    hb.free()
+    tr.close()
     return out
 
 

@@ -78,9 +78,24 @@ def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
                 if ref_hits is not None:   # outputs of the compiled reference recorded in the fixture
                     assert hits.tobytes() == ref_hits.tobytes()
                     assert np.array_equal(frame, ref_image)
+            fused = tr.dev.stats()                      # of the frame above
+            if not strict:
+                # fast-order hit records come from the warp-scheduled ray state machine (rt_machine_b.cu), frames from the
+                # one-ray-per-lane kernel (rt_rtu.cu) unless VORTEX_B200_RTU_MACHINE=2: same records, same frame, same work
+                fused_1 = fused
+                os.environ["VORTEX_B200_RTU_MACHINE"] = "2"
+                try:
+                    assert tr.trace_primary().tobytes() == hits.tobytes()
+                    assert np.array_equal(tr.run(), frame)
+                    mach = tr.dev.stats()
+                    for k in ("rays", "box_tests", "tri_tests", "blas_entered", "shaded_hits"):
+                        assert mach[k] == fused_1[k], (k, mach[k], fused_1[k])
+                    os.environ["VORTEX_B200_RTU_MACHINE"] = "0"
+                    assert tr.trace_primary().tobytes() == hits.tobytes()
+                finally:
+                    os.environ.pop("VORTEX_B200_RTU_MACHINE", None)
             # the three shipped shaders restated against the traceRay/getWork/getAttr/commit shim and dispatched through the
             # SBT: the same frame and the same work as the fused kernel, in either order
-            fused = tr.dev.stats()
             tr.set_program(0)
             try:
                 assert np.array_equal(tr.run(), frame)

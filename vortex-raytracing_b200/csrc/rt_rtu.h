@@ -21,7 +21,10 @@ struct alignas(128) GpuNodeB {
   uint32_t leftFirst;   // QNodeB.leftFirst
   uint32_t leafData;    // QNodeB.leafIdx
   uint32_t flags;       // bit 0: TLAS node (imask == 1); bit 1: leaf; bits 4-7: valid-child mask
-  uint32_t _pad[5];
+  uint32_t _pad[5];     // [1..4] (bytes 112-127): one cursor per child, written by launch_rtu_link for the ray state machine —
+                        // bit 31 TLAS space | kind << 27 | payload: kind 0 inner node (absolute index in its buffer), 1..13 BLAS
+                        // leaf with that many triangles (payload = first triangle), 14 instance (blasIdx), 15 "read the node";
+                        // 0xFFFFFFFF = no child
 };
 static_assert(sizeof(GpuNodeB) == 128, "GpuNodeB");
 
@@ -62,6 +65,28 @@ struct RtuTrace {
   WorkCounters *counters;
   int stats;
 };
+
+// the ray state machine over layout B (rt_machine_b.cu): frames (hits == nullptr) or hit records
+struct RtuMachine {
+  RtuScene scene;
+  KernelArgB arg;
+  uint32_t *out;
+  Partition part;
+  uint32_t camera;
+  WorkCounters *counters;
+  uint32_t *tile_counter;
+  int stats;
+  TileSchedule sched;
+  uint32_t quorum_refill, quorum_inner, chunk;   // as RenderA
+  uint32_t tile_first, tile_end;                 // frames: tiles [tile_first, tile_end) of the rank's enumeration (0, 0 = all)
+  const float *rays;                             // hit records: 6 floats per ray, or nullptr => primary rays
+  HitA *hits;
+  uint64_t count;
+};
+// child cursors of the decoded records: nodes = TLAS records then BLAS records (as decoded), bases = ascending bvh_offset values
+cudaError_t launch_rtu_link(GpuNodeB *nodes, uint64_t n_tlas, uint64_t n_bvh, const uint32_t *bases, uint32_t n_bases, cudaStream_t stream);
+bool rtu_machine_supports(const KernelArgB &a);   // nested mirror rays the slot columns can hold
+int launch_rtu_machine(const RtuMachine &p, int num_sms, cudaStream_t stream);
 
 // scene re-flatten (one launch each): decoded nodes and edge-form triangles
 cudaError_t launch_rtu_decode_nodes(const QNodeB *nodes, GpuNodeB *out, uint64_t n, cudaStream_t stream);

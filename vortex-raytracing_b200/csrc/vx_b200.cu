@@ -116,6 +116,9 @@ public:
     wide_ = nullptr, wide_bases_ = nullptr, wide_bases_host_ = nullptr, wide_valid_ = false;
     if (rtu_nodes_) cudaFree(rtu_nodes_);
     if (rtu_tri_) cudaFree(rtu_tri_);
+    if (rtu_bases_) cudaFree(rtu_bases_);
+    if (rtu_bases_host_) cudaFreeHost(rtu_bases_host_);
+    rtu_bases_ = rtu_bases_host_ = nullptr, rtu_bases_cap_ = 0;
     pipe_free_locked();
     alt_free_locked();
     strips_free_locked();
@@ -986,7 +989,8 @@ private:
     uint64_t tlas_bytes = 0, qbvh_bytes = 0, tri_bytes = 0, blas_bytes = 0, ex_bytes = 0, mat_bytes = 0, tex_bytes = 0;
     uint64_t gen[3] = {0, 0, 0};
     if (resolve(tlas_addr, sizeof(QNodeB), 4, "tlas(q)", &tlas, &tlas_bytes, &gen[0])) return -1;
-    if (resolve(blas_addr, sizeof(BlasNodeB), 4, "blas", &sc->blas, &blas_bytes)) return -1;
+    uint64_t blas_gen = 0;
+    if (resolve(blas_addr, sizeof(BlasNodeB), 4, "blas", &sc->blas, &blas_bytes, &blas_gen)) return -1;
     if (resolve(qbvh_addr, sizeof(QNodeB), 4, "qBvh", &qbvh, &qbvh_bytes, &gen[1])) return -1;
     if (resolve(tri_addr, sizeof(TriA), 4, "tri", &tri, &tri_bytes, &gen[2])) return -1;
     if (resolve(a.triEx_addr, sizeof(TriExB), 4, "triEx", &sc->triEx, &ex_bytes)) return -1;
@@ -996,7 +1000,7 @@ private:
     uint64_t n_tlas = tlas_bytes / sizeof(QNodeB), n_bvh = qbvh_bytes / sizeof(QNodeB), n_tri = tri_bytes / sizeof(TriA);
     if (n_tlas >= (1ull << 30) || n_bvh >= (1ull << 30) || n_tri > 0xFFFFFFFFull) return fail("layout B scene too large");
     if (ex_bytes / sizeof(TriExB) < n_tri) n_tri = ex_bytes / sizeof(TriExB);   // shading indexes triEx by triIdx
-    uint64_t key[9] = {tlas_addr, qbvh_addr, tri_addr, gen[0], gen[1], gen[2], n_tlas, n_bvh, n_tri};
+    uint64_t key[11] = {tlas_addr, qbvh_addr, tri_addr, gen[0], gen[1], gen[2], n_tlas, n_bvh, n_tri, blas_addr, blas_gen};
     if (!rtu_valid_ || memcmp(key, rtu_key_, sizeof(key)) != 0) {
       uint64_t need_nodes = n_tlas + n_bvh;
       if (rtu_nodes_cap_ < need_nodes) {
@@ -1014,7 +1018,40 @@ private:
       CUDA_TRY(launch_rtu_decode_nodes(tlas, rtu_nodes_, n_tlas, stream_));
       CUDA_TRY(launch_rtu_decode_nodes(qbvh, rtu_nodes_ + n_tlas, n_bvh, stream_));
       CUDA_TRY(launch_rtu_gather_tris(tri, rtu_tri_, n_tri, stream_));
-      launches_ += 3, prep_launches_ += 3;
+      {   // child cursors for the ray state machine: a BLAS node's children sit at (its instance's bvh_offset) + leftFirst + k
+        const uint64_t n_blas = blas_bytes / sizeof(BlasNodeB);
+        std::vector<uint8_t> hb(n_blas * sizeof(BlasNodeB));
+        uint64_t bstart = 0;
+        space_.find(blas_addr, 1, &bstart);
+        auto sh = small_shadow_.find(bstart);
+        if (sh != small_shadow_.end() && sh->second.size() >= (blas_addr - bstart) + hb.size()) {
+          memcpy(hb.data(), sh->second.data() + (blas_addr - bstart), hb.size());
+        } else if (!hb.empty()) {
+          CUDA_TRY(cudaMemcpyAsync(hb.data(), sc->blas, hb.size(), cudaMemcpyDeviceToHost, stream_));
+          CUDA_TRY(cudaStreamSynchronize(stream_));
+        }
+        std::vector<uint32_t> bases;
+        for (uint64_t i = 0; i < n_blas; ++i) {
+          uint32_t off;
+          memcpy(&off, hb.data() + i * sizeof(BlasNodeB) + offsetof(BlasNodeB, bvh_offset), 4);
+          if (off < n_bvh) bases.push_back(off);
+        }
+        std::sort(bases.begin(), bases.end());
+        bases.erase(std::unique(bases.begin(), bases.end()), bases.end());
+        if (bases.empty() || bases[0] != 0) bases.insert(bases.begin(), 0u);
+        if (rtu_bases_cap_ < bases.size()) {
+          if (rtu_bases_) cudaFree(rtu_bases_);
+          if (rtu_bases_host_) cudaFreeHost(rtu_bases_host_);
+          rtu_bases_ = rtu_bases_host_ = nullptr, rtu_bases_cap_ = 0;
+          CUDA_TRY(cudaMalloc(&rtu_bases_, bases.size() * 4));
+          CUDA_TRY(cudaMallocHost(&rtu_bases_host_, bases.size() * 4));
+          rtu_bases_cap_ = bases.size();
+        }
+        memcpy(rtu_bases_host_, bases.data(), bases.size() * 4);
+        CUDA_TRY(cudaMemcpyAsync(rtu_bases_, rtu_bases_host_, bases.size() * 4, cudaMemcpyHostToDevice, stream_));
+        CUDA_TRY(launch_rtu_link(rtu_nodes_, n_tlas, n_bvh, rtu_bases_, (uint32_t)bases.size(), stream_));
+      }
+      launches_ += 4, prep_launches_ += 4;
       memcpy(rtu_key_, key, sizeof(key));
       rtu_valid_ = true;
     }
@@ -1045,12 +1082,32 @@ private:
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.part = part_, p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
     p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
-    if (sched_prepare_locked(1, a.dst_width, a.dst_height, true, &p.sched) != 0) return -1;
-    // VX_DCR_B200_RT_KERNEL: 0 = the fused kernel; 2 + n = shader program n through the traceRay/getWork/getAttr/commit
-    // shim (vx_raytrace_b200.cuh; program 0 = the three shipped shaders, rt_rtu_programs.cuh)
+    // VX_DCR_B200_RT_KERNEL: 0 = the fused frame kernel — fast order: the warp-scheduled ray state machine (rt_machine_b.cu),
+    // strict order (or VX_DCR_B200_RT_KERNEL = 1, or more nested mirror rays than a slot holds): one ray per lane (rt_rtu.cu);
+    // 2 + n = shader program n through the traceRay/getWork/getAttr/commit shim (vx_raytrace_b200.cuh; program 0 = the three
+    // shipped shaders, rt_rtu_programs.cuh)
     uint32_t kernel = dcr_get(VX_DCR_B200_RT_KERNEL);
-    int rc = kernel >= 2 ? launch_rtu_program(p, kernel - 2, prop_.multiProcessorCount, stream_)
-                         : launch_rtu_render(p, prop_.multiProcessorCount, stream_);
+    // Measured (tools/quick_rtu_machine.py, profiles/r02_sweep_rtu_machine.txt): on coherent primary rays the state machine is
+    // 7 % SLOWER than one ray per lane (8 522 vs 9 128 Mrays/s at 1080p / 100 K triangles, 7 876 vs 8 447 at 4K / 1 M: with
+    // 4-wide nodes a primary ray makes ~10 visits and 21.5 of 32 lanes are active anyway), on incoherent rays 2.4x faster
+    // (4 203 vs 1 777 Mrays/s).  Frames therefore keep the one-ray-per-lane kernel unless VORTEX_B200_RTU_MACHINE=2 asks for
+    // the machine; hit records (vx_b200_trace_*) use the machine (VORTEX_B200_RTU_MACHINE=0 turns it off).
+    const bool machine = kernel == 0 && !p.strict_order && rtu_machine_supports(a) && p.scene.n_tlas <= (1u << 27) && p.scene.n_bvh <= (1u << 27) &&
+                         p.scene.n_tri <= (1u << 27) && env_u64("VORTEX_B200_RTU_MACHINE", 1) >= 2;
+    if (sched_prepare_locked(1, a.dst_width, a.dst_height, true, &p.sched, /*cost_every_frame=*/!machine) != 0) return -1;
+    int rc;
+    if (machine) {
+      RtuMachine m{};
+      m.scene = p.scene, m.arg = a, m.out = p.out, m.part = part_, m.camera = p.camera, m.counters = counters_, m.tile_counter = tile_counter_;
+      m.stats = stats_on_, m.sched = p.sched;
+      m.quorum_refill = (uint32_t)env_u64("VORTEX_B200_RTU_QUORUM_REFILL", 12), m.quorum_inner = (uint32_t)env_u64("VORTEX_B200_RTU_QUORUM_INNER", 8);
+      m.chunk = 32;
+      if (m.quorum_refill < 2 || m.quorum_refill > 32) m.quorum_refill = 12;
+      if (m.quorum_inner < 1 || m.quorum_inner >= m.quorum_refill) m.quorum_inner = m.quorum_refill / 2;
+      rc = launch_rtu_machine(m, prop_.multiProcessorCount, stream_);
+    } else {
+      rc = kernel >= 2 ? launch_rtu_program(p, kernel - 2, prop_.multiProcessorCount, stream_) : launch_rtu_render(p, prop_.multiProcessorCount, stream_);
+    }
     if (rc < 0) {
       sched_active_ = -1, sched_timed_ = -1;   // no frame ran: nothing to read costs or a trial time from
       return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
@@ -1078,7 +1135,21 @@ private:
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.count = n, p.counters = counters_, p.stats = stats_on_;
     p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
-    int rc = launch_rtu_trace(p, prop_.multiProcessorCount, stream_);
+    int rc;
+    if (!p.strict_order && dcr_get(VX_DCR_B200_RT_KERNEL) != 1 && n < 0xFFFFFFE0ull && p.scene.n_tlas <= (1u << 27) && p.scene.n_bvh <= (1u << 27) &&
+        p.scene.n_tri <= (1u << 27) && env_u64("VORTEX_B200_RTU_MACHINE", 1) != 0) {   // the ray state machine with rays as work items
+      RtuMachine m{};
+      m.scene = p.scene, m.arg = a, m.part = Partition{}, m.camera = p.camera, m.counters = counters_, m.tile_counter = tile_counter_;
+      m.stats = stats_on_, m.rays = p.rays, m.hits = p.hits, m.count = n;
+      m.quorum_refill = (uint32_t)env_u64("VORTEX_B200_RTU_TRACE_QUORUM_REFILL", 16);
+      m.quorum_inner = (uint32_t)env_u64("VORTEX_B200_RTU_TRACE_QUORUM_INNER", 12);
+      m.chunk = 64;
+      if (m.quorum_refill < 2 || m.quorum_refill > 32) m.quorum_refill = 16;
+      if (m.quorum_inner < 1 || m.quorum_inner >= m.quorum_refill) m.quorum_inner = m.quorum_refill / 2;
+      rc = launch_rtu_machine(m, prop_.multiProcessorCount, stream_);
+    } else {
+      rc = launch_rtu_trace(p, prop_.multiProcessorCount, stream_);
+    }
     if (rc < 0) {
       sched_active_ = -1, sched_timed_ = -1;   // no frame ran: nothing to read costs or a trial time from
       return fail("kernel launch failed: %s", cudaGetErrorString((cudaError_t)(-rc)));
@@ -1212,7 +1283,7 @@ private:
     st.identity_loaded = identity, st.order_dirty = false;
     return 0;
   }
-  int sched_prepare_locked(int which, uint32_t W, uint32_t H, bool eligible, TileSchedule *out) {
+  int sched_prepare_locked(int which, uint32_t W, uint32_t H, bool eligible, TileSchedule *out, bool cost_every_frame = false) {
     *out = TileSchedule{};
     sched_active_ = -1, sched_timed_ = -1;
     const uint32_t ntiles = rank_tiles(W, H);
@@ -1267,7 +1338,7 @@ private:
     if (st.frames == 1 || identity != st.identity_loaded || (!identity && st.order_dirty)) {
       if (sched_upload_locked(st, identity) != 0) return -1;
     }
-    const bool measure = phase < 3 || (st.use_order && (which == 1 || (phase & 15u) == 0));
+    const bool measure = phase < 3 || (st.use_order && (cost_every_frame || (phase & 15u) == 0));
     if (identity && !measure) return 0;                    // row-major order, nothing recorded: the kernels' plain path
     out->order = st.d_order, out->cost = nullptr;
     out->group_shift = st.group_shift, out->n_groups = st.n_groups, out->lead = st.lead;
@@ -1363,7 +1434,9 @@ private:
   // layout-B decoded nodes (TLAS then BLAS) and edge-form triangles
   GpuNodeB *rtu_nodes_ = nullptr;
   GpuTri *rtu_tri_ = nullptr;
-  uint64_t rtu_nodes_cap_ = 0, rtu_tri_cap_ = 0, rtu_key_[9] = {0};
+  uint64_t rtu_nodes_cap_ = 0, rtu_tri_cap_ = 0, rtu_key_[11] = {0};
+  uint32_t *rtu_bases_ = nullptr, *rtu_bases_host_ = nullptr;
+  uint64_t rtu_bases_cap_ = 0;
   bool rtu_valid_ = false;
   // run bookkeeping
   WorkCounters *counters_ = nullptr, *h_counters_ = nullptr;
