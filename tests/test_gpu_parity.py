@@ -446,6 +446,7 @@ def test_readback_strips_deliver_the_same_frame():
     karg = sc.setup(w, h)
     tr = tracer_for(sc, karg)
     os.environ["VORTEX_B200_SCHEDULE"] = "0"          # row-major tile order on every frame (an ordered schedule runs as one launch)
+    os.environ["VORTEX_B200_READBACK_MIN_TILES"] = "1000"   # strips normally start at 8K-sized shares (200 000 tiles)
     try:
         for mode in (1, 0):
             tr.set_mode(mode, 0)
@@ -468,4 +469,5 @@ def test_readback_strips_deliver_the_same_frame():
     finally:
         os.environ.pop("VORTEX_B200_READBACK_STRIPS", None)
         os.environ.pop("VORTEX_B200_SCHEDULE", None)
+        os.environ.pop("VORTEX_B200_READBACK_MIN_TILES", None)
         tr.close()

@@ -874,7 +874,10 @@ private:
       const uint32_t strips = (uint32_t)env_u64("VORTEX_B200_READBACK_STRIPS", kStrips);
       // A frame that is read back in strips keeps the row-major tile order (a strip must be a set of whole bands): hiding the
       // framebuffer copy under the tracing is worth more than the ordered schedule's shorter tail.
-      const bool strip_ok = rb && !simple && strips > 1 && my_bands >= 4 * strips && ntiles >= 16384;
+      // Measured (profiles/r02_sweep_readback_strips.txt, one GPU): the 8K frame's end-to-end time is 11.36 ms as one launch,
+      // 10.20 / 10.06 / 9.85 / 9.79 ms in 2 / 4 / 6 / 8 strips; a 1080p frame (0.37 ms of tracing) only loses to the extra
+      // launch tails, so small frames stay one launch.
+      const bool strip_ok = rb && !simple && strips > 1 && my_bands >= 4 * strips && ntiles >= env_u64("VORTEX_B200_READBACK_MIN_TILES", 200000);
       if (sched_prepare_locked(0, a.dst_width, a.dst_height, !simple && p.chunk == 32 && !strip_ok, &p.sched) != 0) return -1;
       if (strip_ok && !p.sched.order) {
         if (strips_init_locked() != 0) return -1;
@@ -1394,7 +1397,7 @@ private:
   uint64_t remote_bytes_ = 0;
   uint8_t *peer_fb_arena_ = nullptr;   // same-process owner of the image (DeviceGroup, VORTEX_B200_FB=peer)
   // strip-pipelined readback
-  static constexpr uint32_t kStrips = 4, kMaxStrips = 8;
+  static constexpr uint32_t kStrips = 8, kMaxStrips = 8;
   uint64_t rb_addr_ = 0, rb_bytes_ = 0;
   uint8_t *rb_host_ = nullptr;
   bool rb_issued_ = false, kend_valid_ = false;
