@@ -720,8 +720,18 @@ def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
     tr.set_order(0)
     tr.launch()
     unit_perf = [rt_unit_perf(tr.dev.stats(), "fast"), rt_unit_perf(wk, "strict")]
-    # the same frame through the traceRay/getWork/getAttr/commit shim with the shipped shaders dispatched by SBT (SURVEY 8f-2)
     tr.dev.enable_stats(False)
+    # BASELINE configs[1] on this layout: primary + shadow rays (VX_DCR_B200_RT_MODE bit 0; the builder-defined extension)
+    tr.set_mode(1)
+    sms = []
+    for i in range(steps + 4):
+        tr.dev.flush_l2()
+        tr.launch()
+        if i >= 4:
+            sms.append(tr.dev.last_kernel_ms())
+    shadow_rays = tr.dev.stats()["rays"]
+    tr.set_mode(0)
+    # the same frame through the traceRay/getWork/getAttr/commit shim with the shipped shaders dispatched by SBT (SURVEY 8f-2)
     tr.set_program(0)
     pms = []
     for i in range(steps + 2):
@@ -743,6 +753,8 @@ def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
            "rt_unit_perf": unit_perf, "ncu": m,
            "shader_program_kernel": {"kernel": "k_rtu_program<ShippedShaders> (fast order)", "kernel_ms": program_ms,
                                      "mrays_per_s": rays / (program_ms * 1e3)},
+           "primary_plus_shadow": {"kernel": "k_rtu_render<ext> (fast order)", "kernel_ms": float(np.mean(sms)), "rays_per_step": shadow_rays,
+                                   "mrays_per_s": shadow_rays / (float(np.mean(sms)) * 1e3)},
            "note": "kernel time only (CUDA events), L2 flushed before every frame; algorithmic work = the reference's trail/short-stack order (strict)"}
     out["incoherent_rays"] = rtu_incoherent()
     if with_cpu:

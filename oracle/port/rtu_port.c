@@ -223,15 +223,16 @@ static int traverse(const rtu_image *im, const rtu_ray *ray, rtu_hit *hit, float
 }
 
 /* one ray through the RT unit with the shipped any-hit shader (always ACCEPT) */
-static void trace_one(const rtu_image *im, const rtu_ray *ray, rtu_hit *hit, rtu_work *w) {
+static void trace_max(const rtu_image *im, const rtu_ray *ray, rtu_hit *hit, float tmax, rtu_work *w) {
   uint32_t trail[RTU_TRAIL];
   rtu_stack stack;
   memset(trail, 0, sizeof(trail));
   memset(&stack, 0, sizeof(stack));
-  hit->dist = RC_LARGE_FLOAT, hit->bx = hit->by = hit->bz = 0.0f, hit->blasIdx = hit->triIdx = 0;
+  hit->dist = tmax, hit->bx = hit->by = hit->bz = 0.0f, hit->blasIdx = hit->triIdx = 0;
   float pending = 0.0f;
   while (!traverse(im, ray, hit, &pending, trail, &stack, w)) hit->dist = pending;      /* commit(ACCEPT), rt_unit.cpp:199-202 */
 }
+static void trace_one(const rtu_image *im, const rtu_ray *ray, rtu_hit *hit, rtu_work *w) { trace_max(im, ray, hit, RC_LARGE_FLOAT, w); }
 
 /* ================================================================ device program: raygen + shaders ================ */
 #pragma pack(push, 1)
@@ -343,11 +344,129 @@ static v3 shade(const rtu_image *im, const rtu_karg *a, const rtu_ray *ray, uint
   return radiance;
 }
 
+/* ---------------------------------------------------------------- extended modes (no reference counterpart) ---------
+ * TraceExt for the RT-unit layout: BASELINE configs 1-3 ask for shadow rays and diffuse bounces, which the reference does not
+ * have on either path.  The definition is the one of the raycast layout (oracle/port/rc_shade.c:rc_trace_ext, kept expression
+ * for expression; the CUDA side is rt_rtu.cu:shade_ext_b), with this layout's own pieces: the RT unit's traversal
+ * (traverse(), i.e. sim/simx/rt_traversal.cpp restated — the only intersection primitive) and the closest-hit shader's
+ * surface evaluation (closest.cpp:61-90: normal, uv, material / texture colour).  mode bit0 = shadow rays, bit1 = diffuse. */
+typedef struct { v3 I, N, texColor; float reflectivity; } rtu_surface;
+static rtu_surface surface_b(const rtu_image *im, const rtu_karg *a, const rtu_ray *ray, const rtu_hit *h) {
+  rtu_blas blas; rtu_triex ex; rtu_material mat;
+  img_read(im, &blas, a->blas_addr + (uint64_t)h->blasIdx * sizeof(rtu_blas), sizeof(blas));
+  img_read(im, &ex, a->triEx_addr + (uint64_t)h->triIdx * sizeof(rtu_triex), sizeof(ex));
+  img_read(im, &mat, a->mat_addr + (uint64_t)ex.texId * sizeof(rtu_material), sizeof(mat));
+  v3 org = V3(ray->ox, ray->oy, ray->oz), dir = V3(ray->dx, ray->dy, ray->dz);
+  rtu_surface s;
+  s.I = vadd(org, vscale(dir, h->dist));
+  v3 N = vadd(vadd(vscale(ex.N1, h->bx), vscale(ex.N2, h->by)), vscale(ex.N0, h->bz));
+  m4 inv; memcpy(inv.c, blas.invTransform, 64);
+  m4 invT = m4_transposed3(&inv);
+  s.N = vnormalize(xform_vec(N, &invT));
+  v2 uv;
+  uv.x = ex.uv1.x * h->bx + ex.uv2.x * h->by + ex.uv0.x * h->bz;
+  uv.y = ex.uv1.y * h->bx + ex.uv2.y * h->by + ex.uv0.y * h->bz;
+  if (mat.diffuse_tex_id >= 0) {
+    uint32_t iu = (uint32_t)(uv.x * mat.tex_width), iv = (uint32_t)(uv.y * mat.tex_height);
+    iu %= mat.tex_width, iv %= mat.tex_height;
+    uint32_t texel;
+    img_read(im, &texel, a->tex_addr + mat.tex_offset + 4ull * (iu + iv * mat.tex_width), 4);
+    s.texColor = rgb8_to_f(texel);
+  } else {
+    s.texColor = mat.diffuse;
+  }
+  s.reflectivity = blas.reflectivity;
+  return s;
+}
+static uint32_t wang_hash_b(uint32_t s) {            /* raytracing/common.h WangHash == raycast/common.h:85-91 */
+  s = (s ^ 61) ^ (s >> 16);
+  s *= 9;
+  s = s ^ (s >> 4);
+  s *= 0x27d4eb2d;
+  s = s ^ (s >> 15);
+  return s;
+}
+static uint32_t random_int_b(uint32_t *s) {          /* xorshift32 (common.h:93-99) */
+  *s ^= *s << 13;
+  *s ^= *s >> 17;
+  *s ^= *s << 5;
+  return *s;
+}
+static float random_float_b(uint32_t *s) { return random_int_b(s) * 2.3283064365387e-10f; }
+
+static v3 trace_ext_b(const rtu_image *im, const rtu_karg *a, const rtu_ray *ray, uint32_t mode, uint32_t *seed, rtu_work *w,
+                      uint64_t *shaded) {
+  rtu_ray cur = *ray;
+  v3 radiance = V3(0, 0, 0);
+  v3 thr = V3(1, 1, 1);
+  for (uint32_t bounce = 0; bounce < a->max_depth; ++bounce) {
+    rtu_hit hit;
+    trace_one(im, &cur, &hit, w);
+    if (hit.dist == RC_LARGE_FLOAT) {
+      radiance = vadd(radiance, vmul(a->background_color, thr));
+      break;
+    }
+    if (shaded) ++*shaded;
+    rtu_surface s = surface_b(im, a, &cur, &hit);
+    v3 dir = V3(cur.dx, cur.dy, cur.dz);
+    v3 Ns = (vdot(s.N, dir) > 0.0f) ? vneg(s.N) : s.N;
+    v3 O = vadd(s.I, vscale(Ns, 0.001f));
+    v3 L = vsub(a->light_pos, s.I);
+    float dist = vlength(L);
+    L = vscale(L, 1.0f / dist);
+    float att = 1.0f / (1.0f + dist * 0.1f);
+    float NdotL = std_maxf(0.0f, vdot(s.N, L));
+    if ((mode & 1u) && NdotL > 0.0f) {
+      v3 Lv = vsub(a->light_pos, O);
+      float d2 = vlength(Lv);
+      v3 D = vscale(Lv, 1.0f / d2);
+      rtu_ray sr = {O.x, O.y, O.z, D.x, D.y, D.z};
+      rtu_hit sh;
+      trace_max(im, &sr, &sh, d2, w);                 /* occluded iff something is hit before the light */
+      if (sh.dist < d2) NdotL = 0.0f;
+    }
+    v3 diffuse = vmul(s.texColor, vadd(a->ambient_color, vscale(sscale(att, a->light_color), NdotL)));
+    if (mode & 2u) {
+      radiance = vadd(radiance, vmul(thr, diffuse));
+      thr = vmul(thr, s.texColor);
+      if (bounce + 1 < a->max_depth) {
+        float px, py, pz, l2;
+        do {
+          px = random_float_b(seed) * 2.0f - 1.0f;
+          py = random_float_b(seed) * 2.0f - 1.0f;
+          pz = random_float_b(seed) * 2.0f - 1.0f;
+          l2 = px * px + py * py + pz * pz;
+        } while (l2 > 1.0f || l2 < 1e-6f);
+        float il = 1.0f / sqrtf(l2);
+        v3 D = vadd(Ns, V3(px * il, py * il, pz * il));
+        float dl2 = vdot(D, D);
+        if (dl2 < 1e-12f) D = Ns;
+        else D = vscale(D, 1.0f / sqrtf(dl2));
+        cur.ox = O.x, cur.oy = O.y, cur.oz = O.z, cur.dx = D.x, cur.dy = D.y, cur.dz = D.z;
+        continue;
+      }
+      break;
+    }
+    radiance = vadd(radiance, vscale(vmul(thr, diffuse), 1 - s.reflectivity));
+    thr = vscale(thr, s.reflectivity);
+    if (s.reflectivity > 0.0f && bounce + 1 < a->max_depth) {
+      v3 R = vnormalize(vsub(dir, vscale(sscale(2.0f, s.N), vdot(s.N, dir))));
+      v3 so = vadd(s.I, vscale(R, 0.001f));
+      cur.ox = so.x, cur.oy = so.y, cur.oz = so.z, cur.dx = R.x, cur.dy = R.y, cur.dz = R.z;
+      continue;
+    }
+    radiance = vadd(radiance, vmul(thr, a->background_color));
+    break;
+  }
+  return radiance;
+}
+
 /* ================================================================ C API (same shapes as oracle/ref_harness) ======== */
 typedef struct {
   rtu_image im; const rtu_karg *arg; uint32_t camera; uint32_t *out;
   const float *rays; uint64_t n; rtu_hit *hits; uint8_t *flags;
   uint32_t next; pthread_mutex_t mu; rtu_work work; uint64_t shaded, total_rays; int count;
+  uint32_t mode;   /* 0 = the shipped shaders; bit0 shadow rays, bit1 diffuse bounces (trace_ext_b) */
 } rtu_job;
 
 static void *trace_worker(void *p) {
@@ -385,7 +504,14 @@ static void *render_worker(void *p) {
     if (y >= a->dst_height) break;
     for (uint32_t x = 0; x < a->dst_width; ++x) {
       rtu_ray r = j->camera ? gen_pinhole(x, y, a) : gen_fixed(x, y, a);
-      v3 c = shade(&j->im, a, &r, 0, j->count ? &w : NULL, &shaded);   /* kernel.cpp:66-81: samples overwrite one payload */
+      v3 c;
+      if (j->mode == 0) {
+        c = shade(&j->im, a, &r, 0, j->count ? &w : NULL, &shaded);    /* kernel.cpp:66-81: samples overwrite one payload */
+      } else {
+        uint32_t seed = wang_hash_b((x + y * a->dst_width) * a->samples_per_pixel + 1);
+        if (seed == 0) seed = 1;
+        c = trace_ext_b(&j->im, a, &r, j->mode, &seed, j->count ? &w : NULL, &shaded);
+      }
       j->out[x + y * a->dst_width] = f_to_rgb8(c);
     }
   }
@@ -425,6 +551,16 @@ void port_rtuh_render(const uint8_t *mem, uint64_t base, uint64_t size, const vo
   rtu_job j; memset(&j, 0, sizeof(j));
   j.im.mem = mem, j.im.base = base, j.im.size = size, j.im.tlas = dcr[0], j.im.blas = dcr[1], j.im.qbvh = dcr[2], j.im.tri = dcr[3];
   j.arg = (const rtu_karg *)karg, j.camera = camera, j.out = out, j.count = work != NULL;
+  run_job(&j, render_worker, threads);
+  if (work) work[0] = j.work.calls, work[1] = j.work.nodes, work[2] = j.work.blas, work[3] = j.work.tris, work[4] = j.work.restarts, work[5] = j.shaded;
+}
+
+/* the same frame with the extended modes (mode bit0 shadow rays, bit1 diffuse bounces) */
+void port_rtuh_render_ext(const uint8_t *mem, uint64_t base, uint64_t size, const void *karg, const uint32_t *dcr, uint32_t camera,
+                          uint32_t mode, uint32_t *out, uint32_t threads, uint64_t *work) {
+  rtu_job j; memset(&j, 0, sizeof(j));
+  j.im.mem = mem, j.im.base = base, j.im.size = size, j.im.tlas = dcr[0], j.im.blas = dcr[1], j.im.qbvh = dcr[2], j.im.tri = dcr[3];
+  j.arg = (const rtu_karg *)karg, j.camera = camera, j.out = out, j.count = work != NULL, j.mode = mode;
   run_job(&j, render_worker, threads);
   if (work) work[0] = j.work.calls, work[1] = j.work.nodes, work[2] = j.work.blas, work[3] = j.work.tris, work[4] = j.work.restarts, work[5] = j.shaded;
 }

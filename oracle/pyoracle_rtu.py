@@ -252,12 +252,19 @@ class RtuPort:
         self.lib.port_rtuh_primary_rays(img.karg.ctypes.data, camera, rays.ctypes.data)
         return rays
 
-    def render(self, img, camera=1, threads=1, want_work=False):
+    def render(self, img, camera=1, threads=1, want_work=False, mode=0):
+        """mode: 0 = the shipped shaders; bit0 shadow rays, bit1 diffuse bounces (the builder-defined extension, rtu_port.c)"""
         w, h = int(img.karg["dst_width"][0]), int(img.karg["dst_height"][0])
         out = np.zeros((h, w), dtype=np.uint32)
         work = np.zeros(6, dtype=np.uint64)
-        self.lib.port_rtuh_render(img.mem.ctypes.data, img.base, len(img.mem), img.karg.ctypes.data, img.dcr.ctypes.data, camera,
-                                  out.ctypes.data, threads, work.ctypes.data if want_work else None)
+        if mode:
+            self.lib.port_rtuh_render_ext.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
+                                                      C.c_void_p, C.c_uint32, C.c_void_p]
+            self.lib.port_rtuh_render_ext(img.mem.ctypes.data, img.base, len(img.mem), img.karg.ctypes.data, img.dcr.ctypes.data, camera,
+                                          int(mode), out.ctypes.data, threads, work.ctypes.data if want_work else None)
+        else:
+            self.lib.port_rtuh_render(img.mem.ctypes.data, img.base, len(img.mem), img.karg.ctypes.data, img.dcr.ctypes.data, camera,
+                                      out.ctypes.data, threads, work.ctypes.data if want_work else None)
         return (out, dict(zip(WORK_NAMES, (int(x) for x in work)))) if want_work else out
 
 

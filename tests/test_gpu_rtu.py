@@ -312,3 +312,47 @@ def test_rtu_schedule_feedback_keeps_the_frame():
                 assert np.array_equal(tr.run(), want), (program, frame)
     finally:
         tr.close()
+
+
+@pytest.mark.parametrize("name", ["cornell64", "multi3_mirror", "hf32"])
+def test_rtu_extended_modes_vs_port(name):
+    """shadow rays / diffuse bounces on the RT-unit layout (VX_DCR_B200_RT_MODE; no reference counterpart): the CUDA kernels
+    against the CPU port's trace_ext_b, whose only intersection primitive is the restated RT-unit traversal.  Strict order
+    (the reference's visiting order) must give the port's frame bit for bit, fast order within 1/255."""
+    mk, w, h, depth, cam = SCENES_B[name]
+    if not R.have_ref():
+        pytest.skip("needs oracle/_ref/libref_rtu.so to build the scene")
+    bufs, karg = R.RtuRef().build_scene(mk(), w, h, max_depth=max(depth, 3))
+    port = R.RtuPort()
+    img = R.Image(bufs, karg)
+    tr = tracer_b(bufs, karg, cam)
+    try:
+        base = tr.run().copy()
+        for mode in (1, 2, 3):
+            want = port.render(img, cam, threads=os.cpu_count() or 1, mode=mode)
+            port.set_fix_tlas_base(1)
+            try:
+                want_fix = port.render(img, cam, threads=os.cpu_count() or 1, mode=mode)
+            finally:
+                port.set_fix_tlas_base(0)
+            tr.set_mode(mode)
+            for strict in (1, 0):
+                tr.set_order(strict)
+                got = tr.run()
+                ref = want if strict else want_fix
+                d = channel_diff(got, ref)
+                assert d <= (0 if strict else 1), (mode, strict, d, int((got != ref).sum()))
+                if strict:
+                    assert np.array_equal(got, want)
+            assert (want != base).any() or name == "one_pixel"      # the mode changes the picture
+            tr.set_program(0)
+            try:
+                with pytest.raises(Exception):
+                    tr.run()                                        # shader programs have no extended modes
+            finally:
+                tr.set_program(None)
+        tr.set_mode(0)
+        tr.set_order(0)
+        assert np.array_equal(tr.run(), base)
+    finally:
+        tr.close()

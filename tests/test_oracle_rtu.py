@@ -128,3 +128,23 @@ def test_quantized_boxes_are_conservative(path):
                 assert (lo <= co + 1e-6).all() and (hi >= co - 1e-6).all()
                 checked += 1
     assert checked > 0
+
+
+@pytest.mark.parametrize("path", GOLDEN[:1], ids=[os.path.basename(p)[:-4] for p in GOLDEN[:1]])
+def test_port_extended_modes_are_deterministic_and_consistent(path):
+    """the builder-defined shadow / diffuse modes of the RT-unit layout (rtu_port.c:trace_ext_b): thread-count independent, mode 0 is
+    the shipped shaders, a shadowed pixel is never brighter than the unshadowed one"""
+    z = np.load(path)
+    g = {k: z[k] for k in z.files}
+    karg = g["karg"].view(R.KARG_B_DT).copy()
+    img = R.Image(g, karg)
+    cam = int(g["camera"])
+    port = R.RtuPort()
+    plain = port.render(img, cam, threads=2)
+    assert np.array_equal(port.render(img, cam, threads=2, mode=0), plain)
+    for mode in (1, 2, 3):
+        a, b = port.render(img, cam, threads=1, mode=mode), port.render(img, cam, threads=4, mode=mode)
+        assert np.array_equal(a, b), mode
+    lit, shadowed = port.render(img, cam, threads=4, mode=0), port.render(img, cam, threads=4, mode=1)
+    for sh in (16, 8, 0):
+        assert (((shadowed >> sh) & 255) <= ((lit >> sh) & 255)).all()

@@ -522,9 +522,82 @@ __device__ __forceinline__ f3 shade_b(const RtuScene &sc, const KernelArgB &a, R
   return color;
 }
 
-// ---------------------------------------------------------------- the pixel loop (kernel.cpp:41-133)
+// Extended modes (no reference counterpart; BASELINE configs 1-3 ask for shadow rays and diffuse bounces): the definition of
+// the raycast layout (rt_raycast.cu:trace_ext == oracle/port/rc_shade.c:rc_trace_ext) with this layout's traversal and surface
+// evaluation, expression for expression the CPU checker's oracle/port/rtu_port.c:trace_ext_b.  mode bit0 shadow, bit1 diffuse.
 template <bool STRICT, bool STATS>
-__global__ void __launch_bounds__(kBlockThreads, STRICT ? 2 : VXB_RTU_MIN_BLOCKS) k_rtu_render(const __grid_constant__ RtuRender p) {
+__device__ __forceinline__ f3 shade_ext_b(const RtuScene &sc, const KernelArgB &a, Ray cur, uint32_t mode, uint32_t &seed, Local &lc,
+                                          uint32_t *stk_e, float *stk_d) {
+  const f3 light_pos = mk3(a.light_pos.x, a.light_pos.y, a.light_pos.z);
+  const f3 light_color = mk3(a.light_color.x, a.light_color.y, a.light_color.z);
+  const f3 ambient = mk3(a.ambient_color.x, a.ambient_color.y, a.ambient_color.z);
+  const f3 background = mk3(a.background_color.x, a.background_color.y, a.background_color.z);
+  f3 radiance = mk3(0, 0, 0);
+  f3 thr = mk3(1, 1, 1);
+  for (uint32_t bounce = 0; bounce < a.max_depth; ++bounce) {
+    Hit hit{kLargeFloat, 0, 0, 0, 0, 0};
+    trace_b<STRICT, STATS>(sc, cur, hit, lc, stk_e, stk_d);
+    if (hit.dist == kLargeFloat) {
+      radiance = radiance + background * thr;
+      break;
+    }
+    if (STATS) lc.shaded++;
+    SurfaceB s = surface_b(sc, cur, hit);
+    f3 Ns = (dot3(s.N, cur.d) > 0.0f) ? neg(s.N) : s.N;
+    f3 O = s.I + Ns * 0.001f;
+    f3 L = light_pos - s.I;
+    float dist = length3(L);
+    L = L * (1.0f / dist);
+    float att = 1.0f / (1.0f + dist * 0.1f);
+    float NdotL = std_max(0.0f, dot3(s.N, L));
+    if ((mode & 1u) && NdotL > 0.0f) {
+      f3 Lv = light_pos - O;
+      float d2 = length3(Lv);
+      f3 D = Lv * (1.0f / d2);
+      Hit sh{d2, 0, 0, 0, 0, 0};                       // occluded iff something is hit before the light
+      trace_b<STRICT, STATS>(sc, Ray{O, D}, sh, lc, stk_e, stk_d);
+      if (sh.dist < d2) NdotL = 0.0f;
+    }
+    f3 diffuse = s.texColor * (ambient + att * light_color * NdotL);
+    if (mode & 2u) {
+      radiance = radiance + thr * diffuse;
+      thr = thr * s.texColor;
+      if (bounce + 1 < a.max_depth) {
+        float px, py, pz, l2;
+        do {
+          px = random_float(seed) * 2.0f - 1.0f;
+          py = random_float(seed) * 2.0f - 1.0f;
+          pz = random_float(seed) * 2.0f - 1.0f;
+          l2 = px * px + py * py + pz * pz;
+        } while (l2 > 1.0f || l2 < 1e-6f);
+        float il = 1.0f / sqrtf(l2);
+        f3 D = Ns + mk3(px * il, py * il, pz * il);
+        float dl2 = dot3(D, D);
+        if (dl2 < 1e-12f) D = Ns;
+        else D = D * (1.0f / sqrtf(dl2));
+        cur.o = O;
+        cur.d = D;
+        continue;
+      }
+      break;
+    }
+    radiance = radiance + thr * diffuse * (1 - s.reflectivity);
+    thr = thr * s.reflectivity;
+    if (s.reflectivity > 0.0f && bounce + 1 < a.max_depth) {
+      f3 R = normalize3(cur.d - 2.0f * s.N * dot3(s.N, cur.d));
+      cur.o = s.I + R * 0.001f;
+      cur.d = R;
+      continue;
+    }
+    radiance = radiance + thr * background;
+    break;
+  }
+  return radiance;
+}
+
+// ---------------------------------------------------------------- the pixel loop (kernel.cpp:41-133)
+template <bool STRICT, bool STATS, bool EXT = false>
+__global__ void __launch_bounds__(kBlockThreads, (STRICT || EXT) ? 2 : VXB_RTU_MIN_BLOCKS) k_rtu_render(const __grid_constant__ RtuRender p) {
   uint32_t stk_e[STRICT ? 1 : kStackB];
   float stk_d[STRICT ? 1 : kStackB];
   const KernelArgB &a = p.arg;
@@ -552,7 +625,14 @@ __global__ void __launch_bounds__(kBlockThreads, STRICT ? 2 : VXB_RTU_MIN_BLOCKS
     if (x < W && y < H) {
       // kernel.cpp:66-81: every sample traces the same ray into the same payload, so one evaluation is the result
       Ray ray = generate_ray_b(x, y, a, p.camera);
-      f3 color = shade_b<STRICT, STATS>(p.scene, a, ray, lc, stk_e, stk_d);
+      f3 color;
+      if (EXT) {
+        uint32_t seed = wang_hash((y * W + x) * a.samples_per_pixel + 1);
+        if (seed == 0) seed = 1;
+        color = shade_ext_b<STRICT, STATS>(p.scene, a, ray, p.mode, seed, lc, stk_e, stk_d);
+      } else {
+        color = shade_b<STRICT, STATS>(p.scene, a, ray, lc, stk_e, stk_d);
+      }
       p.out[y * W + x] = rgb32f_to_rgb8(color);
     }
     __syncwarp();
@@ -617,6 +697,12 @@ cudaError_t launch_rtu_gather_tris(const TriA *tri, GpuTri *gtri, uint64_t n, cu
 }
 
 int launch_rtu_render(const RtuRender &p, int num_sms, cudaStream_t stream) {
+  if (p.mode & 3u) {   // shadow rays / diffuse bounces
+    if (p.strict_order) return p.stats ? launch_persistent(k_rtu_render<true, true, true>, p, num_sms, stream, 0)
+                                       : launch_persistent(k_rtu_render<true, false, true>, p, num_sms, stream, 0);
+    return p.stats ? launch_persistent(k_rtu_render<false, true, true>, p, num_sms, stream, 0)
+                   : launch_persistent(k_rtu_render<false, false, true>, p, num_sms, stream, 0);
+  }
   if (p.strict_order) return p.stats ? launch_persistent(k_rtu_render<true, true>, p, num_sms, stream, 0)
                                      : launch_persistent(k_rtu_render<true, false>, p, num_sms, stream, 0);
   return p.stats ? launch_persistent(k_rtu_render<false, true>, p, num_sms, stream, 0)

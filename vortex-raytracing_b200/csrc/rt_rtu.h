@@ -52,6 +52,7 @@ struct RtuRender {
   uint32_t *tile_counter;
   int stats;
   TileSchedule sched;       // frame-to-frame schedule feedback (rt_raycast.h)
+  uint32_t mode;            // VX_B200_MODE_* bits: shadow rays / diffuse bounces (builder-defined extension, as for layout A)
 };
 
 struct RtuTrace {

@@ -1085,6 +1085,7 @@ private:
     CUDA_TRY(cudaEventRecord(ev_prep_, stream_));
     p.arg = a, p.part = part_, p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
     p.camera = dcr_get(VX_DCR_B200_RT_CAMERA), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
+    p.mode = dcr_get(VX_DCR_B200_RT_MODE) & 3u;
     // VX_DCR_B200_RT_KERNEL: 0 = the fused frame kernel — fast order: the warp-scheduled ray state machine (rt_machine_b.cu),
     // strict order (or VX_DCR_B200_RT_KERNEL = 1, or more nested mirror rays than a slot holds): one ray per lane (rt_rtu.cu);
     // 2 + n = shader program n through the traceRay/getWork/getAttr/commit shim (vx_raytrace_b200.cuh; program 0 = the three
@@ -1095,7 +1096,8 @@ private:
     // 4-wide nodes a primary ray makes ~10 visits and 21.5 of 32 lanes are active anyway), on incoherent rays 2.4x faster
     // (4 203 vs 1 777 Mrays/s).  Frames therefore keep the one-ray-per-lane kernel unless VORTEX_B200_RTU_MACHINE=2 asks for
     // the machine; hit records (vx_b200_trace_*) use the machine (VORTEX_B200_RTU_MACHINE=0 turns it off).
-    const bool machine = kernel == 0 && !p.strict_order && rtu_machine_supports(a) && p.scene.n_tlas <= (1u << 27) && p.scene.n_bvh <= (1u << 27) &&
+    if (p.mode && kernel >= 2) return fail("shadow / diffuse modes are not available for shader programs (VX_DCR_B200_RT_KERNEL >= 2)");
+    const bool machine = kernel == 0 && p.mode == 0 && !p.strict_order && rtu_machine_supports(a) && p.scene.n_tlas <= (1u << 27) && p.scene.n_bvh <= (1u << 27) &&
                          p.scene.n_tri <= (1u << 27) && env_u64("VORTEX_B200_RTU_MACHINE", 1) >= 2;
     if (sched_prepare_locked(1, a.dst_width, a.dst_height, true, &p.sched, /*cost_every_frame=*/!machine) != 0) return -1;
     int rc;

@@ -136,6 +136,10 @@ class RtxTracer:
     def set_order(self, strict_order=False):
         self.dev.dcr_write(vx.VX_DCR_B200_RT_ORDER, int(bool(strict_order)))
 
+    def set_mode(self, mode=0):
+        """VX_DCR_B200_RT_MODE: bit0 shadow rays, bit1 diffuse bounces (the builder-defined extension of BASELINE configs 1-3)"""
+        self.dev.dcr_write(vx.VX_DCR_B200_RT_MODE, int(mode))
+
     def set_program(self, program=None):
         """None = the fused kernel; n = shader program n written against the traceRay/getWork/getAttr/commit shim
         (csrc/vx_raytrace_b200.cuh; 0 = the three shipped shaders, 1 = the cut-out any-hit demo)"""
