@@ -660,6 +660,7 @@ def measure_dynamic_scene(gpus, steps, name="primary_4k_1m"):
     dev.build_bvh(tr.bufs["tri"], ntri, tr.bufs["bvh"], tr.bufs["triIdx"])
     build_ms = dev.stats()["kernel_ms"]
     frame(True)
+    rays = dev.stats()["rays"]
     frame_gpu_tree = out_pinned.numpy().view(np.uint32).copy()
     # the reference's traversal on the GPU-built tree (downloaded bytes)
     gb = dict(bufs)
@@ -669,7 +670,6 @@ def measure_dynamic_scene(gpus, steps, name="primary_4k_1m"):
         gb[n] = a
     par = parity_frames(tr, wl, gb, karg, frame_gpu_tree, gpus, order="fast, GPU-built tree")
     par["pixels_differ_from_host_tree_frame"] = int((frame_gpu_tree != frame_host_tree).sum())
-    rays = dev.stats()["rays"]
     tr.close()
     return {"workload": name + " with the triangles re-uploaded and the BVH rebuilt every frame", "triangles": ntri, "n_gpus": gpus, "steps": steps,
             "gpu_build": {"e2e_ms_per_frame": gpu_ms, "e2e_mrays_per_s": rays / gpu_ms / 1e3, "build_ms": build_ms, "render_kernel_ms": gpu_kernel_ms,

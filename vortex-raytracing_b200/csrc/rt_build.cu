@@ -246,8 +246,39 @@ __global__ void k_emit(const uint2 *__restrict__ children, const uint32_t *__res
   }
 }
 
+// Scratch memory of the builders: one grow-only block per CUDA device, carved up by a bump allocator and kept between builds —
+// cudaMalloc / cudaFree of a dozen arrays cost more than the 1 M-triangle build itself (38 ms vs 11 ms per frame of
+// bench.py's dynamic scene).  Builds of one device are serialised by the runtime's device mutex.
+struct Scratch {
+  uint8_t *base = nullptr;
+  size_t cap = 0, used = 0;
+};
+Scratch g_scratch[64];
+Scratch &scratch() {
+  int d = 0;
+  cudaGetDevice(&d);
+  return g_scratch[d & 63];
+}
+cudaError_t scratch_reserve(size_t bytes) {   // start of a build: everything handed out before is forgotten
+  Scratch &s = scratch();
+  s.used = 0;
+  if (s.cap >= bytes) return cudaSuccess;
+  if (s.base) cudaFree(s.base);
+  s.base = nullptr, s.cap = 0;
+  const size_t want = bytes + bytes / 8 + (1 << 20);
+  cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&s.base), want);
+  if (e == cudaSuccess) s.cap = want;
+  return e;
+}
 template <class T>
-cudaError_t alloc(T **p, size_t count) { return cudaMalloc(reinterpret_cast<void **>(p), count * sizeof(T)); }
+cudaError_t alloc(T **p, size_t count) {
+  Scratch &s = scratch();
+  const size_t bytes = (count * sizeof(T) + 255) & ~size_t(255);
+  if (s.used + bytes > s.cap) return cudaErrorMemoryAllocation;
+  *p = reinterpret_cast<T *>(s.base + s.used);
+  s.used += bytes;
+  return cudaSuccess;
+}
 
 }  // namespace
 
@@ -264,8 +295,7 @@ struct Lbvh {
   const uint32_t *order = nullptr;   // sorted position -> triangle (points into vals / vals2)
   int launches = 0;
   void release() {
-    cudaFree(cb), cudaFree(leaf_box), cudaFree(int_box), cudaFree(keys), cudaFree(keys2), cudaFree(vals), cudaFree(vals2);
-    cudaFree(parent_int), cudaFree(parent_leaf), cudaFree(arrived), cudaFree(children), cudaFree(tmp), cudaFree(sah);
+    // scratch memory: nothing to free (see Scratch)
   }
 };
 
@@ -277,6 +307,13 @@ struct Lbvh {
 cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t, SahParams sp = SahParams{0.f, 1.f, 1u}) {
   size_t tmp_bytes = 0;
   cudaError_t e = cudaSuccess;
+  {   // everything this build (and, for layout B, its emission passes) takes from the scratch block
+    size_t sort_bytes = 0;
+    cub::DoubleBuffer<uint64_t> k0(nullptr, nullptr);
+    cub::DoubleBuffer<uint32_t> v0(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, k0, v0, (int)n, 0, 63, stream);
+    VXB_TRY(scratch_reserve((size_t)n * 256 + sort_bytes + (1 << 16)));
+  }
   VXB_TRY(alloc(&t.cb, 6));
   VXB_TRY(alloc(&t.leaf_box, n));
   VXB_TRY(alloc(&t.int_box, n));
@@ -292,7 +329,7 @@ cudaError_t lbvh_tree(const float *tf, uint32_t n, cudaStream_t stream, Lbvh &t,
   cub::DoubleBuffer<uint64_t> dk(t.keys, t.keys2);
   cub::DoubleBuffer<uint32_t> dv(t.vals, t.vals2);
   VXB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
-  VXB_TRY(cudaMalloc(&t.tmp, tmp_bytes ? tmp_bytes : 16));
+  VXB_TRY(alloc(reinterpret_cast<uint8_t **>(&t.tmp), tmp_bytes ? tmp_bytes : 16));
   if (e != cudaSuccess) return e;
   const unsigned blocks = (n + 255) / 256;
   k_init_bounds<<<1, 32, 0, stream>>>(t.cb);
@@ -482,7 +519,7 @@ int build_qbvh4(TriA *tri, TriExB *triEx, uint32_t n, uint32_t tri_first, QNodeB
   VXB_TRY(alloc(&box_dev, 6));
   if (triEx) VXB_TRY(alloc(&ex_tmp, (size_t)n * 4));
   VXB_TRY(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, nchild, first, (int)(n_int ? n_int : 1), stream));
-  VXB_TRY(cudaMalloc(&scan_tmp, scan_bytes ? scan_bytes : 16));
+  VXB_TRY(alloc(reinterpret_cast<uint8_t **>(&scan_tmp), scan_bytes ? scan_bytes : 16));
   if (e == cudaSuccess && n_int) {
     const unsigned ib = (n_int + 255) / 256;
     k_b_parity<<<ib, 256, 0, stream>>>(t.parent_int, n_int, even);
@@ -515,12 +552,17 @@ int build_qbvh4(TriA *tri, TriExB *triEx, uint32_t n, uint32_t tri_first, QNodeB
     VXB_TRY(cudaStreamSynchronize(stream));
   }
   t.release();
-  cudaFree(even), cudaFree(nchild), cudaFree(first), cudaFree(idx_int), cudaFree(idx_leaf), cudaFree(tri_tmp), cudaFree(box_dev);
-  cudaFree(ex_tmp), cudaFree(scan_tmp);
+  // scratch memory: nothing to free (see Scratch)
   if (nodes_used) *nodes_used = total;
   if (launches) *launches = t.launches;
   return e == cudaSuccess ? 0 : -(int)e;
 }
 #undef VXB_TRY
+
+void build_release_scratch() {
+  Scratch &s = scratch();
+  if (s.base) cudaFree(s.base);
+  s = Scratch{};
+}
 
 }  // namespace vxb

@@ -17,4 +17,6 @@ int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, u
 // root_box6 (host memory, may be null) receives the mesh's bounds for the TLAS.
 int build_qbvh4(TriA *tri, TriExB *triEx, uint32_t n, uint32_t tri_first, QNodeB *qbvh, uint64_t qbvh_capacity, cudaStream_t stream,
                 uint32_t *nodes_used, float *root_box6, int *launches);
+// frees the current device's builder scratch block (kept between builds)
+void build_release_scratch();
 }  // namespace vxb

@@ -109,6 +109,7 @@ public:
       for (auto &e : stage_ev_) if (e) cudaEventDestroy(e), e = nullptr;
       stage_ = nullptr, stage_next_ = 0;
     }
+    build_release_scratch();
     if (gtri_) cudaFree(gtri_);
     if (wide_) cudaFree(wide_);
     if (wide_bases_) cudaFree(wide_bases_);
