@@ -81,6 +81,15 @@ def test_group_device_equals_single_gpu_and_oracle(env):
         assert two.trace_rays(rays).tobytes() == want.tobytes()
         assert two.dev.stats()["rays"] == len(rays)
         assert two.trace_rays_host(rays).tobytes() == want.tobytes()
+        # a partial read of the hit records gathers the pieces on GPU 0 first (peer copies, or ncclSend/ncclRecv)
+        rb, hb = two.dev.upload_bytes(rays), two.dev.mem_alloc(len(rays) * 24)
+        two.dev.trace_rays(two.args, rb, len(rays), hb)
+        two.dev.ready_wait()
+        tail = np.zeros(len(rays) - 20_000, dtype=want.dtype)
+        hb.copy_from_dev(tail, src_offset=20_000 * 24)
+        assert tail.tobytes() == want[20_000:].tobytes()
+        rb.free()
+        hb.free()
         assert hit_parity(two.trace_primary(), one.trace_primary())["mismatch"] == 0
         assert_hit_gates(hit_parity(want, sc.trace_rays(rays, threads=oracle.hw_threads())), False)
         # a partial upload into a replicated buffer reaches every GPU
