@@ -877,8 +877,10 @@ private:
       // framebuffer copy under the tracing is worth more than the ordered schedule's shorter tail.
       // Measured (profiles/r02_sweep_readback_strips.txt, one GPU): the 8K frame's end-to-end time is 11.36 ms as one launch,
       // 10.20 / 10.06 / 9.85 / 9.79 ms in 2 / 4 / 6 / 8 strips; a 1080p frame (0.37 ms of tracing) only loses to the extra
-      // launch tails, so small frames stay one launch.
-      const bool strip_ok = rb && !simple && strips > 1 && my_bands >= 4 * strips && ntiles >= env_u64("VORTEX_B200_READBACK_MIN_TILES", 200000);
+      // launch tails, so small frames stay one launch.  Eight GPUs (129 600 tiles each, profiles/r02_scale/strips_n8.txt): 3.92 ms as
+      // one launch per GPU, 3.90 / 3.44 / 3.33 ms in 2 / 4 / 8 strips — the copies (95 GB/s for the whole box) take longer than the
+      // tracing there, so hiding the tracing under them pays although the strips give up the ordered schedule.
+      const bool strip_ok = rb && !simple && strips > 1 && my_bands >= 4 * strips && ntiles >= env_u64("VORTEX_B200_READBACK_MIN_TILES", 100000);
       if (sched_prepare_locked(0, a.dst_width, a.dst_height, !simple && p.chunk == 32 && !strip_ok, &p.sched) != 0) return -1;
       if (strip_ok && !p.sched.order) {
         if (strips_init_locked() != 0) return -1;
