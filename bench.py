@@ -454,7 +454,8 @@ def measure_frames(name, gpus, steps, warmup, kernel=0, cpu=False, parity=True, 
     dev.enable_stats(False)
     unit_perf = [rt_unit_perf(work_own, "fast"), rt_unit_perf(work_ref, "strict")]
     abytes, aflops = algorithmic_work(work_ref, W * H)
-    roof = roofline_block(name, "k_render_a" if kernel == 1 else "k_render_m", k_ms, gpus, work_ref, work_own, abytes, aflops,
+    kname = "k_render_a" if kernel == 1 else ("k_render_m" if os.environ.get("VORTEX_B200_DIRECT", "1") == "0" else "k_render_direct")
+    roof = roofline_block(name, kname, k_ms, gpus, work_ref, work_own, abytes, aflops,
                           own_work(work_own, W * H), dev.caps(0x3))
 
     par = None

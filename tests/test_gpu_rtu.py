@@ -92,8 +92,14 @@ def check_scene(bufs, karg, cam, ref_hits=None, ref_image=None):
                         assert mach[k] == fused_1[k], (k, mach[k], fused_1[k])
                     os.environ["VORTEX_B200_RTU_MACHINE"] = "0"
                     assert tr.trace_primary().tobytes() == hits.tobytes()
+                    os.environ["VORTEX_B200_RTU_DIRECT"] = "0"      # rt_rtu.cu's k_rtu_render (nodes without child cursors)
+                    assert np.array_equal(tr.run(), frame)
+                    old = tr.dev.stats()
+                    for k in ("rays", "box_tests", "tri_tests", "blas_entered", "shaded_hits"):
+                        assert old[k] == fused_1[k], (k, old[k], fused_1[k])
                 finally:
                     os.environ.pop("VORTEX_B200_RTU_MACHINE", None)
+                    os.environ.pop("VORTEX_B200_RTU_DIRECT", None)
             # the three shipped shaders restated against the traceRay/getWork/getAttr/commit shim and dispatched through the
             # SBT: the same frame and the same work as the fused kernel, in either order
             tr.set_program(0)

@@ -41,8 +41,12 @@ def frame_ms(tr, n=12):
 for n, w, h in ((224, 1920, 1080), (708, 3840, 2160)):
     tr = scene(n, w, h)
     os.environ["VORTEX_B200_RTU_MACHINE"] = "0"
+    os.environ["VORTEX_B200_RTU_DIRECT"] = "0"
     ms, rays = frame_ms(tr)
     print(f"{w}x{h} {2 * n * n} tris: one ray per lane {rays / ms / 1e3:.0f} Mrays/s", flush=True)
+    os.environ["VORTEX_B200_RTU_DIRECT"] = "1"
+    ms, rays = frame_ms(tr)
+    print(f"{w}x{h} {2 * n * n} tris: one ray per lane over cursor-carrying records (k_rtu_direct) {rays / ms / 1e3:.0f} Mrays/s", flush=True)
     os.environ["VORTEX_B200_RTU_MACHINE"] = "2"      # 2 = frames through the state machine too (default: hit records only)
     for refill, inner in ((12, 8), (8, 4), (16, 8), (16, 12), (24, 12), (24, 16), (28, 20), (32, 24)):
         os.environ["VORTEX_B200_RTU_QUORUM_REFILL"], os.environ["VORTEX_B200_RTU_QUORUM_INNER"] = str(refill), str(inner)

@@ -44,6 +44,8 @@ def raw_probe(total_mb=160):
 
 print(f"N={N} raw link probe (one slice per GPU, {160 // N} MB each, all concurrently): " +
       ", ".join(f"{k} {v[0]:.1f} GB/s ({v[1]:.3f} ms)" for k, v in raw_probe().items()), flush=True)
+print(f"N={N} raw link probe, 36 MB in all (the size of the tri buffer; {36 / N:.1f} MB per GPU): " +
+      ", ".join(f"{k} {v[0]:.1f} GB/s ({v[1]:.3f} ms)" for k, v in raw_probe(36).items()), flush=True)
 
 tracer_mod = bench.pkg("tracer")
 wl = bench.WORKLOADS[name]

@@ -711,6 +711,81 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_m(cons
     }
 }
 
+// ---- frames, one pixel per lane, over the same 4-wide records and step functions (fast order; RenderA::direct) ----
+// The A/B of round 2 on layout B (rt_machine_b.cu) showed that for coherent rays the warp scheduling costs more than the
+// divergence it removes; this kernel is that experiment for layout A: persistent warps pull 8x4 tiles, every lane runs its
+// pixel's rays (primary, shadow, bounces, samples) to completion through step_wide / step_other / post.
+template <uint32_t MODE, bool STATS>
+__global__ void __launch_bounds__(kBlockThreads, VXB_MIN_BLOCKS) k_render_direct(const __grid_constant__ RenderA p) {
+  constexpr uint32_t kCols = (MODE & 1u) ? C_SHADOW_END : C_BASE_END;
+  __shared__ float s_cols[kCols * kBlockThreads];
+  uint32_t stk_e[kMachineStack];
+  float stk_d[kMachineStack];
+  const Stk stk{stk_e, stk_d, nullptr};
+  const Smem sm{s_cols, threadIdx.x};
+  const KernelArgA &a = p.arg;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t W = a.dst_width, H = a.dst_height;
+  const uint32_t tcols = (W + kTileW - 1) / kTileW;
+  const uint32_t band_rows = p.part.band_rows, world = p.part.world, rank = p.part.rank;
+  const uint32_t nbands_total = (H + band_rows - 1) / band_rows;
+  const uint32_t nbands = nbands_total > rank ? (nbands_total - rank + world - 1) / world : 0;
+  const uint32_t tiles_per_band = (band_rows / kTileH) * tcols;
+  const uint32_t all_tiles = nbands * tiles_per_band;
+  const uint32_t ntiles = p.tile_end ? min(p.tile_end, all_tiles) - p.tile_first : all_tiles;
+  Lane L;
+  L.st = S_EMPTY, L.sp = 0, L.base = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.nodes = p.scene.nodes, L.wide = reinterpret_cast<const uint8_t *>(p.scene.wide), L.blas = 0;
+  L.o = L.d = L.id = mk3(0, 0, 0);
+  L.steps = 0;
+  Local lc{0, 0, 0, 0, 0};
+  for (;;) {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(p.tile_counter, 1u);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= ntiles) break;
+    uint32_t grp;
+    const uint32_t tile = sched_tile(p.sched, t + p.tile_first, all_tiles, grp);
+    const uint32_t band_local = tile / tiles_per_band, r = tile % tiles_per_band;
+    const uint32_t trow = r / tcols, tcol = r % tcols;
+    const uint32_t x = tcol * kTileW + (lane & (kTileW - 1));
+    const uint32_t y = (band_local * world + rank) * band_rows + trow * kTileH + (lane / kTileW);
+    uint32_t steps = 0;
+    if (x < W && y < H) {
+      const uint32_t pix = y * W + x;
+      sm.u(C_PIX) = pix;
+      sm.put3(C_COLX, mk3(0, 0, 0));
+      begin_sample<MODE>(L, sm, p, pix, 0, lc);
+      do {
+        while ((L.st & S_MASK) == S_TRAV) {
+          simt_step<STATS>(lc);
+          ++steps;
+          if (is_inner(L)) step_wide<STATS, 0, false>(L, (L.st & F_NAN) != 0, stk, lc, nullptr);
+          else step_other<false, STATS, 0, false>(L, sm, p.scene, stk, lc, false);
+        }
+        post<MODE, STATS, false>(L, sm, p, lc);
+      } while ((L.st & S_MASK) != S_EMPTY);
+    }
+    if (p.sched.cost && grp != 0xFFFFFFFFu) {   // most traversal steps spent on one pixel of this group
+      steps = __reduce_max_sync(0xffffffffu, steps);
+      if (lane == 0) atomicMax(p.sched.cost + grp, steps);
+    }
+  }
+  __syncwarp();
+  flush_counters(p.counters, lc, STATS);
+}
+
+template <uint32_t MODE, bool STATS>
+int launch_d(const RenderA &p, int num_sms, cudaStream_t stream) {
+  auto kern = k_render_direct<MODE, STATS>;
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, 0);
+  if (e != cudaSuccess) return -(int)e;
+  if (per_sm < 1) per_sm = 1;
+  kern<<<num_sms * per_sm, kBlockThreads, 0, stream>>>(p);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? 1 : -(int)e;
+}
+
 template <uint32_t MODE, bool STRICT, bool STATS>
 int launch_m(const RenderA &p, int num_sms, cudaStream_t stream) {
   // the cost-recording build runs only on the frames that re-measure the schedule (p.sched.cost set), and never for rays
@@ -811,6 +886,14 @@ int launch_trace_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
 
 int launch_render_machine(const RenderA &p, int num_sms, cudaStream_t stream) {
   if (!p.strict_order && !p.scene.wide) return -(int)cudaErrorInvalidValue;   // fast order walks the 4-wide records
+  if (!p.strict_order && p.direct) {
+    switch (p.mode & 3u) {
+      case 0: return p.stats ? launch_d<0, true>(p, num_sms, stream) : launch_d<0, false>(p, num_sms, stream);
+      case 1: return p.stats ? launch_d<1, true>(p, num_sms, stream) : launch_d<1, false>(p, num_sms, stream);
+      case 2: return p.stats ? launch_d<2, true>(p, num_sms, stream) : launch_d<2, false>(p, num_sms, stream);
+      default: return p.stats ? launch_d<3, true>(p, num_sms, stream) : launch_d<3, false>(p, num_sms, stream);
+    }
+  }
   if (p.strict_order) return p.stats ? launch_mm<true, true>(p, num_sms, stream) : launch_mm<true, false>(p, num_sms, stream);
   return p.stats ? launch_mm<false, true>(p, num_sms, stream) : launch_mm<false, false>(p, num_sms, stream);
 }

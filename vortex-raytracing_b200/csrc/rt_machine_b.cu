@@ -526,6 +526,64 @@ __global__ void __launch_bounds__(kBlockThreads, VXB_RTUM_MIN_BLOCKS) k_rtu_mach
     }
 }
 
+// ---- frames, one ray per lane, over the same cursor-carrying records ----
+// Coherent primary rays leave the state machine nothing to schedule (measured: 7 % slower than one ray per lane), but the child
+// cursors pay on their own: a leaf or an instance node is never fetched (2 of the ~10 node reads of a primary ray), and the
+// per-lane loop below is the machine's own step functions without the warp scheduling.  Persistent warps pull 8x4 tiles like
+// rt_rtu.cu's k_rtu_render; the tile's clock count feeds the schedule feedback the same way.
+template <bool STATS>
+__global__ void __launch_bounds__(kBlockThreads, VXB_RTUM_MIN_BLOCKS) k_rtu_direct(const __grid_constant__ RtuMachine p) {
+  __shared__ float s_cols[C_END * kBlockThreads];
+  uint32_t stk_e[kStackM];
+  float stk_d[kStackM];
+  const Stk stk{stk_e, stk_d, nullptr};
+  const Smem sm{s_cols, threadIdx.x};
+  const KernelArgB &a = p.arg;
+  const uint32_t W = a.dst_width, H = a.dst_height;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t tcols = (W + kTileW - 1) / kTileW;
+  const uint32_t band_rows = p.part.band_rows, world = p.part.world, rank = p.part.rank;
+  const uint32_t nbands_total = (H + band_rows - 1) / band_rows;
+  const uint32_t nbands = nbands_total > rank ? (nbands_total - rank + world - 1) / world : 0;
+  const uint32_t tiles_per_band = (band_rows / kTileH) * tcols;
+  const uint32_t ntiles = nbands * tiles_per_band;
+  Lane L;
+  L.st = S_EMPTY, L.sp = 0, L.base = 0, L.cur = 0, L.dist = kLargeFloat, L.bx = L.by = 0.f, L.hblas = L.htri = 0, L.blas = 0, L.steps = 0;
+  L.o = L.d = L.id = mk3(0, 0, 0);
+  Local lc{};
+  for (;;) {
+    uint32_t tile = 0;
+    if (lane == 0) tile = atomicAdd(p.tile_counter, 1u);
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+    if (tile >= ntiles) break;
+    uint32_t grp;
+    tile = sched_tile(p.sched, tile, ntiles, grp);
+    const uint32_t t0 = (uint32_t)clock();
+    uint32_t band_local = tile / tiles_per_band, r = tile % tiles_per_band;
+    uint32_t trow = r / tcols, tcol = r % tcols;
+    uint32_t x = tcol * kTileW + (lane & (kTileW - 1));
+    uint32_t y = (band_local * world + rank) * band_rows + trow * kTileH + (lane / kTileW);
+    if (x < W && y < H) {
+      sm.u(C_PIX) = y * W + x;
+      sm.u(C_DEPTH) = 0u;
+      Ray ray = generate_ray_b(x, y, a, p.camera);
+      start_ray(L, sm, ray.o, ray.d, lc);
+      do {   // one ray after the other of this pixel's path: the primary ray, then the nested mirror rays POST queues
+        while ((L.st & S_MASK) == S_TRAV) {
+          simt_step<STATS>(lc);
+          if (is_inner(L)) visit4<STATS, 0>(L, p.scene.gbvh + (L.cur & kPay), (L.st & F_NAN) != 0, stk, lc);
+          else step_other<STATS, 0>(L, sm, p.scene, stk, lc);
+        }
+        post<kModeFrame, STATS, false>(L, sm, p, lc);
+      } while ((L.st & S_MASK) != S_EMPTY);
+    }
+    __syncwarp();
+    if (lane == 0 && grp != 0xFFFFFFFFu && p.sched.cost) atomicMax(p.sched.cost + grp, (uint32_t)clock() - t0);   // longest tile of the group
+  }
+  __syncwarp();
+  flush_counters(p.counters, lc, STATS);
+}
+
 // ---- child cursors of the decoded records (once per upload) ----
 __global__ void k_rtu_link(GpuNodeB *__restrict__ nodes, uint64_t n_tlas, uint64_t n_bvh, const uint32_t *__restrict__ bases, uint32_t n_bases) {
   uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -590,6 +648,17 @@ cudaError_t launch_rtu_link(GpuNodeB *nodes, uint64_t n_tlas, uint64_t n_bvh, co
 }
 
 bool rtu_machine_supports(const KernelArgB &a) { return a.max_depth <= kMachineBounce + 1; }
+
+int launch_rtu_direct(const RtuMachine &p, int num_sms, cudaStream_t stream) {
+  auto kern = p.stats ? k_rtu_direct<true> : k_rtu_direct<false>;
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockThreads, 0);
+  if (e != cudaSuccess) return -(int)e;
+  if (per_sm < 1) per_sm = 1;
+  kern<<<num_sms * per_sm, kBlockThreads, 0, stream>>>(p);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? 1 : -(int)e;
+}
 
 int launch_rtu_machine(const RtuMachine &p, int num_sms, cudaStream_t stream) {
   if (p.hits) {

@@ -77,6 +77,8 @@ struct RenderA {
   uint64_t count;
   const uint32_t *perm;     // hit-record mode: work item k traces ray perm[k] (launch_ray_order), or nullptr = identity
   uint32_t n_blas;          // instances in the blas buffer (the -DVXB_SMEM_TOP=1 A/B variant stages the tree top only for one)
+  uint32_t direct;          // frames, fast order: 1 = one pixel per lane over the 4-wide records (k_render_direct), 0 = the
+                            // warp-scheduled state machine
   uint32_t tile_first, tile_end;   // frame modes: this launch renders tiles [tile_first, tile_end) of the rank's enumeration
                                    // (0, 0 = all of them); strips of one frame are launched back to back so that the finished
                                    // bands of one strip travel to the host while the next strip is traced

@@ -88,6 +88,8 @@ struct RtuMachine {
 cudaError_t launch_rtu_link(GpuNodeB *nodes, uint64_t n_tlas, uint64_t n_bvh, const uint32_t *bases, uint32_t n_bases, cudaStream_t stream);
 bool rtu_machine_supports(const KernelArgB &a);   // nested mirror rays the slot columns can hold
 int launch_rtu_machine(const RtuMachine &p, int num_sms, cudaStream_t stream);
+// frames with one ray per lane over the same cursor-carrying records (no warp scheduling); p.sched.cost in SM clocks per tile
+int launch_rtu_direct(const RtuMachine &p, int num_sms, cudaStream_t stream);
 
 // scene re-flatten (one launch each): decoded nodes and edge-form triangles
 cudaError_t launch_rtu_decode_nodes(const QNodeB *nodes, GpuNodeB *out, uint64_t n, cudaStream_t stream);

@@ -858,6 +858,10 @@ private:
       p.mode = dcr_get(VX_DCR_B200_RT_MODE), p.strict_order = dcr_get(VX_DCR_B200_RT_ORDER);
       p.counters = counters_, p.tile_counter = tile_counter_, p.stats = stats_on_;
       p.n_blas = n_blas_launch;
+      // Fast-order frames: one pixel per lane over the 4-wide records (k_render_direct) — measured against the warp-scheduled
+      // state machine on one B200 (profiles/r02_sweep_direct_a.txt): cfg1 11 284 vs 7 264 Mrays/s, cfg3 12 786 vs 7 783, 4K
+      // primary 11 759 vs 8 519, cfg2 (4 diffuse bounces) 4 905 vs 4 773.  VORTEX_B200_DIRECT=0 selects the state machine.
+      p.direct = (uint32_t)env_u64("VORTEX_B200_DIRECT", 1);
       p.quorum_refill = (uint32_t)env_u64("VORTEX_B200_QUORUM_REFILL", 12);
       p.quorum_inner = (uint32_t)env_u64("VORTEX_B200_QUORUM_INNER", 8);
       p.chunk = (uint32_t)env_u64("VORTEX_B200_CHUNK", 32);
@@ -1103,9 +1107,12 @@ private:
     if (p.mode && kernel >= 2) return fail("shadow / diffuse modes are not available for shader programs (VX_DCR_B200_RT_KERNEL >= 2)");
     const bool machine = kernel == 0 && p.mode == 0 && !p.strict_order && rtu_machine_supports(a) && p.scene.n_tlas <= (1u << 27) && p.scene.n_bvh <= (1u << 27) &&
                          p.scene.n_tri <= (1u << 27) && env_u64("VORTEX_B200_RTU_MACHINE", 1) >= 2;
+    // ... and the same records walked one ray per lane (k_rtu_direct): the default for fast-order frames
+    const bool direct = !machine && kernel == 0 && p.mode == 0 && !p.strict_order && rtu_machine_supports(a) && p.scene.n_tlas <= (1u << 27) &&
+                        p.scene.n_bvh <= (1u << 27) && p.scene.n_tri <= (1u << 27) && env_u64("VORTEX_B200_RTU_DIRECT", 1) != 0;
     if (sched_prepare_locked(1, a.dst_width, a.dst_height, true, &p.sched, /*cost_every_frame=*/!machine) != 0) return -1;
     int rc;
-    if (machine) {
+    if (machine || direct) {
       RtuMachine m{};
       m.scene = p.scene, m.arg = a, m.out = p.out, m.part = part_, m.camera = p.camera, m.counters = counters_, m.tile_counter = tile_counter_;
       m.stats = stats_on_, m.sched = p.sched;
@@ -1113,7 +1120,7 @@ private:
       m.chunk = 32;
       if (m.quorum_refill < 2 || m.quorum_refill > 32) m.quorum_refill = 12;
       if (m.quorum_inner < 1 || m.quorum_inner >= m.quorum_refill) m.quorum_inner = m.quorum_refill / 2;
-      rc = launch_rtu_machine(m, prop_.multiProcessorCount, stream_);
+      rc = machine ? launch_rtu_machine(m, prop_.multiProcessorCount, stream_) : launch_rtu_direct(m, prop_.multiProcessorCount, stream_);
     } else {
       rc = kernel >= 2 ? launch_rtu_program(p, kernel - 2, prop_.multiProcessorCount, stream_) : launch_rtu_render(p, prop_.multiProcessorCount, stream_);
     }
