@@ -746,7 +746,7 @@ def quick_run_rtu(n=224, w=1920, h=1080, steps=20, with_cpu=True):
     abytes = 52 * wk["box_tests"] + 52 * wk["blas_entered"] + 36 * wk["tri_tests"] + 156 * wk["shaded_hits"] + 4 * w * h
     k_ms = float(np.mean(ms))
     m = ncu_metrics("rtu_1080p_primary_100k")
-    out = {"mrays_per_s": rays / (k_ms * 1e3), "kernel": "k_rtu_render (fast order)", "kernel_ms": k_ms, "steps": steps, "rays_per_step": rays,
+    out = {"mrays_per_s": rays / (k_ms * 1e3), "kernel": "k_rtu_direct (fast order; one ray per lane over the cursor-carrying records)", "kernel_ms": k_ms, "steps": steps, "rays_per_step": rays,
            "strict_order_kernel_ms": strict_ms, "host_bvh4_build_s": round(build_s, 3),
            "algorithmic_bytes_per_ray": abytes / max(1, rays), "algorithmic_gbs_reference_order": abytes / (k_ms * 1e-3) / 1e9,
            "work_per_ray": {"nodes": wk["box_tests"] / max(1, rays), "tri_tests": wk["tri_tests"] / max(1, rays),
