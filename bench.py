@@ -914,7 +914,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (the parity checker still runs)")
-    ap.add_argument("--kernel", type=int, default=0, help="layout-A render kernel: 0 = ray state machine (default), 1 = one pixel per lane")
+    ap.add_argument("--kernel", type=int, default=0, help="layout-A render kernel (VX_DCR_B200_RT_KERNEL): 0 = default, 1 = round 1's one-pixel-per-lane BVH2 walk; env VORTEX_B200_DIRECT=0 = ray state machine")
     ap.add_argument("--fb", default=None, choices=["local", "peer"], help="N > 1: each GPU keeps its bands (default) / kernels store into GPU 0's framebuffer")
     ap.add_argument("--collective", default=None, choices=["peer", "nccl"], help="N > 1: scene replication by peer copies (default) / ncclAllGather")
     ap.add_argument("--extra", type=int, default=1, help="also measure the secondary workloads (config.secondary_workloads)")

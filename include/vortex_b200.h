@@ -79,7 +79,7 @@ typedef void *vx_buffer_h;
 #define VX_DCR_B200_RT_LAYOUT 0x0F1  /* 0 = infer from argument size (192 -> A, 216 -> B), 1 = A, 2 = B */
 #define VX_DCR_B200_RT_ORDER 0x0F2   /* 0 = near-first BLAS order (fast), 1 = the reference's far-first order (strict) */
 #define VX_DCR_B200_RT_CAMERA 0x0F3  /* layout B only: 0 = the hard-coded camera of raytracing/kernel.cpp:28-39, 1 = kernel_arg_t pinhole camera */
-#define VX_DCR_B200_RT_KERNEL 0x0F4  /* layout A render kernel: 0 = warp-scheduled ray state machine (default), 1 = one pixel per lane */
+#define VX_DCR_B200_RT_KERNEL 0x0F4  /* render kernel: 0 = default (layout A: one pixel per lane over the 4-wide records, env VORTEX_B200_DIRECT=0 selects the warp-scheduled ray state machine; layout B: one ray per lane over the cursor-carrying records), 1 = round 1's one-pixel-per-lane kernels (BVH2 walk / records without cursors), 2 + n = layout-B shader program n */
 
 #define VX_B200_MODE_SHADOW 0x1u
 #define VX_B200_MODE_DIFFUSE 0x2u

@@ -1,4 +1,6 @@
-// vx_b200.cu — the b200 runtime backend: a vx_device over one B200, and the C ABI of include/vortex_b200.h.
+// vx_b200.cu — the b200 runtime backend: class Device = everything that belongs to ONE B200 (arena, stream, caches, launches),
+// DeviceGroup (vx_group.inc) = what a vx_device_h points at, one Device per GPU of the box it spans, and the C ABI of
+// include/vortex_b200.h.
 //
 // Mirrors the role of runtime/simx/vortex.cpp (class vx_device, :49-636) + runtime/common/callbacks.inc
 // (the handle/glue layer, :14-225) + runtime/stub/utils.cpp (upload helpers, :25-122) of the reference,

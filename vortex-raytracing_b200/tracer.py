@@ -128,7 +128,7 @@ class Tracer:
     def set_mode(self, mode=0, strict_order=False, kernel=None):
         self.dev.dcr_write(vx.VX_DCR_B200_RT_MODE, int(mode))
         self.dev.dcr_write(vx.VX_DCR_B200_RT_ORDER, int(bool(strict_order)))
-        if kernel is not None:   # 0 = ray state machine (default), 1 = one pixel per lane
+        if kernel is not None:   # 0 = default (one pixel per lane over the 4-wide records), 1 = round 1's BVH2-walk kernel
             self.dev.dcr_write(vx.VX_DCR_B200_RT_KERNEL, int(kernel))
 
     def close(self):
