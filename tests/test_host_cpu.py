@@ -174,3 +174,31 @@ def test_host_builder_large_parallel_equals_serial():
     ba, bb = a.buffers(), b.buffers()
     for n in ("bvh", "triIdx", "tlas", "blas"):
         assert ba[n].tobytes() == bb[n].tobytes(), n
+
+
+def test_parity_helpers_generate_the_reference_primary_rays():
+    """vortex-raytracing_b200/parity.py: the numpy GenerateRay used by bench.py's parity block equals the oracle's own primary rays
+    (render.h:190-208) bit for bit on a small frame, and the band sampler hits every GPU of a round-robin deal"""
+    import importlib
+    par = importlib.import_module("vortex-raytracing_b200.parity")
+    po = importlib.import_module("oracle.pyoracle")
+    orc = po.best()
+    sc = orc.scene_create([scenes.heightfield(8)])
+    karg = sc.setup(96, 56)
+    _, rays = sc.trace_primary(want_rays=True, threads=2)
+    mine = par.primary_rays(karg, range(56))
+    assert mine.shape == rays.shape
+    assert np.array_equal(mine[:, :3], rays[:, :3])
+    assert np.abs(mine[:, 3:] - rays[:, 3:]).max() <= 1.2e-7          # same formula in float32; the last bit may differ
+    bench = importlib.import_module("bench")
+    for gpus in (1, 2, 4, 8):
+        bands = bench.sample_bands(4320, gpus)
+        assert len(bands) == 8 and len({b % gpus for b in bands}) == min(gpus, 8)
+    a = np.zeros(4, dtype=po.HIT_DT)
+    a["dist"] = [1.0, 2.0, 1e30, 3.0]
+    a["triIdx"] = [1, 2, 0, 3]
+    b = a.copy()
+    b["triIdx"][0] = 9                                                  # same t, other triangle: a tie
+    b["dist"][3], b["triIdx"][3] = 4.0, 7                               # other t: not a tie
+    hp = par.hit_parity(b, a)
+    assert (hp["mismatch"], hp["ties"], hp["non_tie"]) == (2, 1, 1)
