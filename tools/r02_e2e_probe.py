@@ -122,5 +122,6 @@ run()
 print(f"download ({W * H * 4 / 1e6:.1f} MB): {phase(download):.3f} ms")
 print(f"full sequence: {phase(full):.3f} ms")
 dev.set_readback(tr.out, out_pinned.data_ptr(), W * H * 4)
+print(f"start+wait with readback (no uploads): {phase(run):.3f} ms   (kernel_ms {dev.stats()['kernel_ms']:.3f})")
 print(f"full sequence with readback: {phase(full):.3f} ms   (launches per step {dev.stats()['kernel_launches']}, kernel_ms {dev.stats()['kernel_ms']:.3f})")
 tr.close()

@@ -879,7 +879,12 @@ private:
       const bool rb = rb_host_ && rb_addr_ == a.dst_addr && rb_bytes_ >= (uint64_t)a.dst_width * a.dst_height * 4 && !remote_fb_ && !peer_fb_arena_;
       const uint32_t tiles_per_band = (part_.band_rows / 4) * ((a.dst_width + 7) / 8), ntiles = rank_tiles(a.dst_width, a.dst_height);
       const uint32_t my_bands = tiles_per_band ? ntiles / tiles_per_band : 0;
-      const uint32_t strips = (uint32_t)env_u64("VORTEX_B200_READBACK_STRIPS", kStrips);
+      // strip count and taper (strip k+1 = taper % of strip k; only the last strip's copy is exposed).  One GPU, 8K frame
+      // (profiles/r02_sweep_readback_taper.txt): start + wait + download 4.46 ms in 8 equal strips, 4.41 in 16, 4.31-4.34 in 16
+      // strips tapered by 90 %; 70 % makes the first strip too long (4.55).  The defaults of a group's GPUs stay 8 equal strips.
+      const bool big_single = part_.world == 1 && my_bands >= 512;
+      const uint32_t strips = (uint32_t)env_u64("VORTEX_B200_READBACK_STRIPS", big_single ? 16 : kStrips);
+      const uint32_t taper = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(env_u64("VORTEX_B200_READBACK_TAPER", big_single ? 90 : 100), 25), 100);
       // A frame that is read back in strips keeps the row-major tile order (a strip must be a set of whole bands): hiding the
       // framebuffer copy under the tracing is worth more than the ordered schedule's shorter tail.
       // Measured (profiles/r02_sweep_readback_strips.txt, one GPU): the 8K frame's end-to-end time is 11.36 ms as one launch,
@@ -897,8 +902,21 @@ private:
         CUDA_TRY(cudaStreamWaitEvent(aux_stream_, ev_strip_[kMaxStrips], 0));
         rc = 0;
         const uint32_t S = std::min<uint32_t>(strips, kMaxStrips);
+        uint32_t edge[kMaxStrips + 1];
+        {
+          const double q = taper / 100.0;
+          double total = 0, w = 1, acc = 0;
+          for (uint32_t k = 0; k < S; k++) total += w, w *= q;
+          w = 1, edge[0] = 0;
+          for (uint32_t k = 0; k < S; k++) {   // every strip keeps at least one band (my_bands >= 4 * S)
+            acc += w, w *= q;
+            const uint32_t want = taper == 100 ? (uint32_t)((uint64_t)my_bands * (k + 1) / S) : (uint32_t)(my_bands * (acc / total) + 0.5);
+            edge[k + 1] = std::max<uint32_t>(edge[k] + 1, std::min<uint32_t>(my_bands - (S - 1 - k), want));
+          }
+          edge[S] = my_bands;
+        }
         for (uint32_t k = 0; k < S && rc >= 0; k++) {
-          const uint32_t b0 = (uint32_t)((uint64_t)my_bands * k / S), b1 = (uint32_t)((uint64_t)my_bands * (k + 1) / S);
+          const uint32_t b0 = edge[k], b1 = edge[k + 1];
           cudaStream_t st = (k & 1) ? aux_stream_ : stream_;
           RenderA q = p;
           q.tile_first = b0 * tiles_per_band, q.tile_end = b1 * tiles_per_band, q.tile_counter = strip_counters_ + k;
@@ -1412,7 +1430,7 @@ private:
   uint64_t remote_bytes_ = 0;
   uint8_t *peer_fb_arena_ = nullptr;   // same-process owner of the image (DeviceGroup, VORTEX_B200_FB=peer)
   // strip-pipelined readback
-  static constexpr uint32_t kStrips = 8, kMaxStrips = 8;
+  static constexpr uint32_t kStrips = 8, kMaxStrips = 16;
   uint64_t rb_addr_ = 0, rb_bytes_ = 0;
   uint8_t *rb_host_ = nullptr;
   bool rb_issued_ = false, kend_valid_ = false;
