@@ -257,6 +257,18 @@ int vx_b200_trace_rays_host(vx_device_h hdevice, vx_buffer_h harguments, const v
 int vx_b200_build_bvh(vx_device_h hdevice, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h hbvh,
                       uint64_t node_first, vx_buffer_h htriIdx, uint64_t slot_first, uint64_t *nodes_used);
 
+/* vx_b200_build_bvh without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, same kernels and the same bytes in `hbvh` / `htriIdx` as vx_b200_build_bvh, but the builder's scratch arrays
+ * (Morton keys, sort buffers, radix-tree links, boxes) live in a file-scope static __device__ array of 8 MiB that every GPU
+ * which loads the library holds until exit, so tri_count is limited to 65 536 triangles: larger counts are rejected with an
+ * error (vx_b200_last_error names the limit) and nothing is written.  The call itself performs no cudaMalloc / cudaFree /
+ * event or stream creation and calls no allocating library routine.  All calls on one GPU share the array, which keeps the
+ * previous call's contents (what must start at zero is cleared by the call): calls that overlap on the GPU — two host
+ * threads building on the same GPU through different device handles — race; one handle serialises its calls.  Synchronous. */
+int vx_b200_build_bvh_static(vx_device_h hdevice, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h hbvh,
+                             uint64_t node_first, vx_buffer_h htriIdx, uint64_t slot_first, uint64_t *nodes_used);
+
 /* GPU BVH build for layout B (the RT unit's buffers): the same radix tree collapsed to a BVH4 and quantized into
  * bvh_quantized_node_t records (52 B, raytracing/common.h:58-67; what BVH::build + quantize leave in qBvh, raytracing/bvh.cpp:
  * 38-258) written to `hqbvh` from node index node_first; node indices inside the records are relative to node_first, which is

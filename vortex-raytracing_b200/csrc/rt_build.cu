@@ -566,3 +566,101 @@ void build_release_scratch() {
 }
 
 }  // namespace vxb
+
+// ------------------------------------------------------------------------------------------------ build without allocation
+// vx_b200_build_bvh_static: the layout-A build for callers that must not allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  Its scratch arrays are carved from this array, which every GPU that loads the library holds until
+// exit; all calls on one GPU share it (calls that overlap on the GPU would race) and it keeps the previous call's contents.
+static __device__ __align__(256) uint8_t g_build_static_scratch[vxb::kBuildStaticScratchBytes];
+
+namespace vxb {
+namespace {
+uint8_t *g_static_base[64];   // per CUDA device: where the array lives THERE (the symbol itself is only a host-side handle)
+struct Bump {
+  uint8_t *base;
+  size_t cap, used;
+  template <class T>
+  cudaError_t take(T **p, size_t count) {
+    const size_t bytes = (count * sizeof(T) + 255) & ~size_t(255);
+    if (used + bytes > cap) return cudaErrorMemoryAllocation;
+    *p = reinterpret_cast<T *>(base + used);
+    used += bytes;
+    return cudaSuccess;
+  }
+};
+}  // namespace
+
+int build_lbvh_static(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches,
+                      float c_trav, uint32_t max_leaf) {
+  if (n == 0 || n > kBuildStaticMaxTris) return -(int)cudaErrorInvalidValue;
+  if (max_leaf < 1) max_leaf = 1;
+  if (max_leaf > 14) max_leaf = 14;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return -(int)e;
+  uint8_t *&base = g_static_base[dev & 63];
+  if (!base) {   // once per device, with that device current
+    uint8_t *ptr = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void **>(&ptr), g_build_static_scratch);
+    if (e != cudaSuccess) return -(int)e;
+    base = ptr;
+  }
+  Bump b{base, kBuildStaticScratchBytes, 0};
+  const SahParams sp{c_trav, 1.0f, max_leaf};
+  const float *tf = reinterpret_cast<const float *>(tri);
+  float *cb = nullptr;
+  Box3 *leaf_box = nullptr, *int_box = nullptr;
+  uint64_t *keys = nullptr, *keys2 = nullptr;
+  uint32_t *vals = nullptr, *vals2 = nullptr, *parent_int = nullptr, *parent_leaf = nullptr, *arrived = nullptr;
+  uint2 *children = nullptr;
+  SahInfo *sah = nullptr;
+  uint8_t *tmp = nullptr;
+#define VXB_TRY_S(x)                 \
+  do {                               \
+    if (e == cudaSuccess) e = (x);   \
+  } while (0)
+  VXB_TRY_S(b.take(&cb, 6));
+  VXB_TRY_S(b.take(&leaf_box, n));
+  VXB_TRY_S(b.take(&int_box, n));
+  VXB_TRY_S(b.take(&keys, n));
+  VXB_TRY_S(b.take(&keys2, n));
+  VXB_TRY_S(b.take(&vals, n));
+  VXB_TRY_S(b.take(&vals2, n));
+  VXB_TRY_S(b.take(&parent_int, n));
+  VXB_TRY_S(b.take(&parent_leaf, n));
+  VXB_TRY_S(b.take(&arrived, n));
+  VXB_TRY_S(b.take(&children, n));
+  if (sp.max_leaf > 1) VXB_TRY_S(b.take(&sah, n));
+  cub::DoubleBuffer<uint64_t> dk(keys, keys2);
+  cub::DoubleBuffer<uint32_t> dv(vals, vals2);
+  size_t tmp_bytes = 0;
+  VXB_TRY_S(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
+  VXB_TRY_S(b.take(&tmp, tmp_bytes ? tmp_bytes : 16));
+  if (e != cudaSuccess) return -(int)e;
+  int nl = 0;
+  const unsigned blocks = (n + 255) / 256;
+  k_init_bounds<<<1, 32, 0, stream>>>(cb);                       // the array keeps the last call's contents:
+  VXB_TRY_S(cudaMemsetAsync(arrived, 0, (size_t)n * 4, stream));   // bounds and arrival flags start from scratch
+  k_leaf_boxes<<<blocks, 256, 0, stream>>>(tf, n, leaf_box, cb);
+  k_morton<<<blocks, 256, 0, stream>>>(tf, n, cb, keys, vals);
+  nl += 3;
+  VXB_TRY_S(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, (int)n, 0, 63, stream));
+  nl += 1;
+  const uint32_t *order = dv.Current();
+  if (n > 1 && e == cudaSuccess) {
+    k_radix_tree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(dk.Current(), (int)n, children, parent_int, parent_leaf);
+    k_fit<<<blocks, 256, 0, stream>>>(children, parent_int, parent_leaf, order, leaf_box, int_box, arrived, n, sah, sp);
+    nl += 2;
+  }
+  if (e == cudaSuccess) {
+    k_emit<<<blocks, 256, 0, stream>>>(children, order, leaf_box, int_box, n, nodes, triIdx, tri_first, sah, parent_int);
+    nl += 1;
+  }
+  VXB_TRY_S(cudaGetLastError());
+  VXB_TRY_S(cudaStreamSynchronize(stream));
+#undef VXB_TRY_S
+  if (launches) *launches = nl;
+  return e == cudaSuccess ? 0 : -(int)e;
+}
+
+}  // namespace vxb

@@ -17,6 +17,13 @@ int build_lbvh(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, u
 // root_box6 (host memory, may be null) receives the mesh's bounds for the TLAS.
 int build_qbvh4(TriA *tri, TriExB *triEx, uint32_t n, uint32_t tri_first, QNodeB *qbvh, uint64_t qbvh_capacity, cudaStream_t stream,
                 uint32_t *nodes_used, float *root_box6, int *launches);
+// build_lbvh without any allocation: the scratch arrays come from a static __device__ array of kBuildStaticScratchBytes (per GPU,
+// held from library load to exit), which limits it to kBuildStaticMaxTris triangles.  Same kernels, same result as build_lbvh.
+// Calls on one GPU share the array: they must not overlap on the GPU.
+constexpr uint32_t kBuildStaticMaxTris = 65536;
+constexpr size_t kBuildStaticScratchBytes = 8u << 20;   // 104 B per triangle in 11 arrays + the sort's histograms
+int build_lbvh_static(const TriA *tri, uint32_t n, BvhNodeA *nodes, uint32_t *triIdx, uint32_t tri_first, cudaStream_t stream, int *launches,
+                      float c_trav = 1.0f, uint32_t max_leaf = 4);
 // frees the current device's builder scratch block (kept between builds)
 void build_release_scratch();
 }  // namespace vxb

@@ -464,6 +464,38 @@ public:
     if (nodes_used) *nodes_used = 2 * tri_count - 1;
     return 0;
   }
+  // vx_b200_build_bvh_static: build_bvh with the builder's scratch in a static device array — no allocation of any kind here
+  // (no events either: the statistics of this call carry no time)
+  int build_bvh_static(uint64_t tri_addr, uint64_t tri_count, uint64_t tri_first, uint64_t bvh_addr, uint64_t idx_addr, uint64_t *nodes_used) {
+    std::lock_guard<std::mutex> g(mu_);
+    CUDA_TRY(cudaSetDevice(cuda_dev_));
+    if (tri_count == 0) return fail("vx_b200_build_bvh_static: bad triangle count");
+    if (tri_count > kBuildStaticMaxTris)
+      return fail("vx_b200_build_bvh_static: %llu triangles exceed the static scratch array's limit of %u (use vx_b200_build_bvh)",
+                  (unsigned long long)tri_count, kBuildStaticMaxTris);
+    if (run_pending_) {
+      CUDA_TRY(cudaStreamSynchronize(stream_));
+      if (finish_run_locked() != 0) return -1;
+    }
+    const TriA *tri = nullptr;
+    BvhNodeA *nodes = nullptr;
+    uint32_t *idx = nullptr;
+    if (resolve(tri_addr, tri_count * sizeof(TriA), 4, "tri", &tri)) return -1;
+    if (resolve(bvh_addr, (2 * tri_count - 1) * sizeof(BvhNodeA), 16, "bvh", &nodes)) return -1;
+    if (resolve(idx_addr, tri_count * 4, 4, "triIdx", &idx)) return -1;
+    int nl = 0;
+    const char *ct = getenv("VORTEX_B200_BUILD_CTRAV");
+    const float c_trav = ct && *ct ? (float)atof(ct) : 1.0f;
+    int rc = build_lbvh_static(tri, (uint32_t)tri_count, nodes, idx, (uint32_t)tri_first, stream_, &nl, c_trav,
+                               (uint32_t)env_u64("VORTEX_B200_BUILD_MAX_LEAF", 4));
+    if (rc != 0) return fail("vx_b200_build_bvh_static: %s", cudaGetErrorString((cudaError_t)(-rc)));
+    uint64_t start = 0;
+    if (auto *b = space_.find(bvh_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
+    if (auto *b = space_.find(idx_addr, 1, &start)) b->write_gen = ++generation_, small_shadow_.erase(start);
+    stats_.kernel_launches = (uint64_t)nl, stats_.prep_launches = 0, stats_.kernel_ms = 0, stats_.prep_ms = 0;
+    if (nodes_used) *nodes_used = 2 * tri_count - 1;
+    return 0;
+  }
   int build_qbvh(uint64_t tri_addr, uint64_t tri_count, uint64_t tri_first, uint64_t ex_addr, uint64_t qbvh_addr, uint64_t capacity,
                  uint64_t *nodes_used, float *root_box6) {
     std::lock_guard<std::mutex> g(mu_);
@@ -1779,6 +1811,19 @@ VXB_EXPORT int vx_b200_build_bvh(vx_device_h h, vx_buffer_h htri, uint64_t tri_f
     return fail("vx_b200_build_bvh: range outside a buffer");
   return ((Device *)h)->build_bvh(t->addr + tri_first * sizeof(vxb::TriA), tri_count, tri_first, b->addr + node_first * sizeof(vxb::BvhNodeA),
                                   i->addr + slot_first * 4, nodes_used);
+}
+VXB_EXPORT int vx_b200_build_bvh_static(vx_device_h h, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h hbvh,
+                                        uint64_t node_first, vx_buffer_h htriIdx, uint64_t slot_first, uint64_t *nodes_used) {
+  if (!h || !htri || !hbvh || !htriIdx) return -1;
+  auto t = (Buffer *)htri, b = (Buffer *)hbvh, i = (Buffer *)htriIdx;
+  if (tri_count > vxb::kBuildStaticMaxTris)
+    return fail("vx_b200_build_bvh_static: %llu triangles exceed the static scratch array's limit of %u (use vx_b200_build_bvh)",
+                (unsigned long long)tri_count, vxb::kBuildStaticMaxTris);
+  if (tri_count == 0 || (tri_first + tri_count) * sizeof(vxb::TriA) > t->size ||
+      (node_first + 2 * tri_count - 1) * sizeof(vxb::BvhNodeA) > b->size || (slot_first + tri_count) * 4 > i->size)
+    return fail("vx_b200_build_bvh_static: range outside a buffer");
+  return ((Device *)h)->build_bvh_static(t->addr + tri_first * sizeof(vxb::TriA), tri_count, tri_first,
+                                         b->addr + node_first * sizeof(vxb::BvhNodeA), i->addr + slot_first * 4, nodes_used);
 }
 VXB_EXPORT int vx_b200_build_qbvh(vx_device_h h, vx_buffer_h htri, uint64_t tri_first, uint64_t tri_count, vx_buffer_h htriEx,
                                   vx_buffer_h hqbvh, uint64_t node_first, uint64_t *nodes_used, float *root_box6) {

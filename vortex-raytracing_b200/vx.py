@@ -24,7 +24,7 @@ EXPORTS = (
     "vx_dev_init vx_dev_open vx_dev_close vx_dev_caps vx_mem_alloc vx_mem_reserve vx_mem_free vx_mem_access "
     "vx_mem_address vx_mem_info vx_copy_to_dev vx_copy_from_dev vx_start vx_ready_wait vx_dcr_read vx_dcr_write "
     "vx_mpm_query vx_upload_kernel_bytes vx_upload_kernel_file vx_upload_bytes vx_upload_file vx_dump_perf "
-    "vx_b200_select_device vx_b200_select_gpus vx_b200_set_readback vx_b200_flush_l2 vx_b200_set_partition vx_b200_build_bvh vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_mark_written vx_b200_probe_gather vx_b200_stream vx_b200_last_kernel_ms "
+    "vx_b200_select_device vx_b200_select_gpus vx_b200_set_readback vx_b200_flush_l2 vx_b200_set_partition vx_b200_build_bvh vx_b200_build_bvh_static vx_b200_build_qbvh vx_b200_export_buffer vx_b200_set_remote_framebuffer vx_b200_device_ptr vx_b200_mark_written vx_b200_probe_gather vx_b200_stream vx_b200_last_kernel_ms "
     "vx_b200_enable_stats vx_b200_get_stats vx_b200_trace_primary vx_b200_trace_rays vx_b200_trace_rays_host vx_b200_last_error"
 ).split()
 
@@ -70,6 +70,7 @@ def lib():
             "vx_b200_trace_primary": [H, B, B], "vx_b200_trace_rays": [H, B, B, u64, B],
             "vx_b200_trace_rays_host": [H, B, C.c_void_p, u64, C.c_void_p],
             "vx_b200_build_bvh": [H, B, u64, u64, B, u64, B, u64, C.POINTER(u64)],
+            "vx_b200_build_bvh_static": [H, B, u64, u64, B, u64, B, u64, C.POINTER(u64)],
             "vx_b200_build_qbvh": [H, B, u64, u64, B, B, u64, C.POINTER(u64), C.POINTER(C.c_float)],
             "vx_b200_export_buffer": [B, vp, C.POINTER(u64)], "vx_b200_set_remote_framebuffer": [H, vp, u64, u64],
         }
@@ -227,6 +228,13 @@ class Device:
         used = C.c_uint64()
         _check(lib().vx_b200_build_bvh(self.h, tri.h, tri_first, tri_count, bvh.h, node_first, tri_idx.h, slot_first, C.byref(used)),
                "vx_b200_build_bvh")
+        return used.value
+
+    def build_bvh_static(self, tri, tri_count, bvh, tri_idx, tri_first=0, node_first=0, slot_first=0):
+        """build_bvh without any allocation (scratch in a static device array; at most 65 536 triangles, larger counts raise)."""
+        used = C.c_uint64()
+        _check(lib().vx_b200_build_bvh_static(self.h, tri.h, tri_first, tri_count, bvh.h, node_first, tri_idx.h, slot_first, C.byref(used)),
+               "vx_b200_build_bvh_static")
         return used.value
 
     def build_qbvh(self, tri, tri_count, tri_ex, qbvh, tri_first=0, node_first=0):
