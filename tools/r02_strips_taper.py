@@ -62,10 +62,11 @@ def full():
 print(f"{name} N={N}: plain start+wait {phase(run):.3f} ms, + download {phase(run_dl):.3f} ms, full sequence {phase(full):.3f} ms", flush=True)
 dev.set_readback(tr.out, out_pinned.data_ptr(), W * H * 4)
 ref = None
-VARIANTS = [(8, 100), (12, 100), (16, 100), (8, 85), (8, 70), (12, 85), (16, 90), (16, 80)]   # (strips, taper %)
-for strips, taper in VARIANTS:
+VARIANTS = [(16, 90, 0), (16, 90, 2), (16, 90, 1), (16, 90, 2), (8, 100, 0), (8, 100, 2), (16, 80, 2), (12, 90, 2)]   # (strips, taper %, order: 0 top-down, 1 bottom-up, 2 by feedback)
+for strips, taper, order in VARIANTS:
     os.environ["VORTEX_B200_READBACK_STRIPS"] = str(strips)
     os.environ["VORTEX_B200_READBACK_TAPER"] = str(taper)
+    os.environ["VORTEX_B200_READBACK_ORDER"] = str(order)
     a, b = phase(run_dl), phase(full)
     out_pinned.zero_()   # the comparison below must see THIS variant's copy
     run_dl()
@@ -73,5 +74,5 @@ for strips, taper in VARIANTS:
     img = out_pinned.clone()
     same = "first" if ref is None else ("same image" if bool((img == ref).all()) else "IMAGE DIFFERS")
     ref = img if ref is None else ref
-    print(f"strips {strips:2d} taper {taper:3d}: start+wait+download {a:.3f} ms, full sequence {b:.3f} ms  (kernel_ms {dev.stats()['kernel_ms']:.3f}, launches {dev.stats()['kernel_launches']}, {same})", flush=True)
+    print(f"strips {strips:2d} taper {taper:3d} order {order}: start+wait+download {a:.3f} ms, full sequence {b:.3f} ms  (kernel_ms {dev.stats()['kernel_ms']:.3f}, launches {dev.stats()['kernel_launches']}, {same})", flush=True)
 tr.close()

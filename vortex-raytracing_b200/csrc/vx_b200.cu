@@ -721,7 +721,7 @@ private:
     CUDA_TRY(cudaMemsetAsync(counters_, 0, sizeof(WorkCounters), stream_));
     CUDA_TRY(cudaMemsetAsync(tile_counter_, 0, sizeof(uint32_t), stream_));
     launches_ = 0, prep_launches_ = 0;
-    rb_issued_ = false, kend_valid_ = false;
+    rb_issued_ = false, kend_valid_ = false, half_valid_ = false;
     CUDA_TRY(cudaEventRecord(ev_begin_, stream_));
     return 0;
   }
@@ -743,7 +743,13 @@ private:
     run_pending_ = false;
     float ms_total = 0, ms_prep = 0;
     CUDA_TRY(cudaEventElapsedTime(&ms_total, ev_begin_, kend_valid_ ? ev_kend_ : ev_end_));
-    kend_valid_ = false;
+    if (kend_valid_ && half_valid_) {   // strip-pipelined frame: share of the kernel time taken by the strips that went first
+      float ms_half = 0, ms_all = 0;
+      CUDA_TRY(cudaEventElapsedTime(&ms_half, ev_prep_, ev_half_));
+      CUDA_TRY(cudaEventElapsedTime(&ms_all, ev_prep_, ev_kend_));
+      if (ms_all > 0 && ms_half / ms_all > strip_half_share_ + 0.08f) strip_reverse_ = !strip_reverse_;
+    }
+    kend_valid_ = false, half_valid_ = false;
     CUDA_TRY(cudaEventElapsedTime(&ms_prep, ev_begin_, ev_prep_));
     stats_.rays = h_counters_->rays;
     stats_.box_tests = h_counters_->box_tests;
@@ -947,8 +953,19 @@ private:
           }
           edge[S] = my_bands;
         }
+        // Which end of the image goes first: a strip's copy can only start when its kernel has ended, so strips that trace
+        // quickly (sky, a far ground plane) should go FIRST — at the end their copies would queue behind each other after the
+        // last kernel (profiles/r02_sweep_readback_taper.txt, timeline).  The previous strip-pipelined frame tells: if the half
+        // of the bands that went first took 8 points more than its share of the kernel time, the order is turned round (and
+        // stays: the same half then reads 8 points less).
+        const uint64_t order_env = env_u64("VORTEX_B200_READBACK_ORDER", 2);   // 0 top-down, 1 bottom-up, 2 by feedback
+        const bool rev = order_env == 2 ? strip_reverse_ : order_env == 1;
+        strip_reverse_ = rev;
+        uint32_t k_half = 0;   // the strip with which half of the bands have been launched (strips may be tapered)
+        while (k_half + 1 < S && 2 * edge[k_half + 1] < my_bands) ++k_half;
+        strip_half_share_ = (float)edge[k_half + 1] / (float)my_bands;
         for (uint32_t k = 0; k < S && rc >= 0; k++) {
-          const uint32_t b0 = edge[k], b1 = edge[k + 1];
+          const uint32_t b0 = rev ? my_bands - edge[k + 1] : edge[k], b1 = rev ? my_bands - edge[k] : edge[k + 1];
           cudaStream_t st = (k & 1) ? aux_stream_ : stream_;
           RenderA q = p;
           q.tile_first = b0 * tiles_per_band, q.tile_end = b1 * tiles_per_band, q.tile_counter = strip_counters_ + k;
@@ -957,8 +974,12 @@ private:
           if (r < 0) { rc = r; break; }
           rc += r;
           CUDA_TRY(cudaEventRecord(ev_strip_[k], st));
+          if (k == k_half) {
+            CUDA_TRY(cudaEventRecord(ev_half_, st));
+            half_valid_ = true;
+          }
           CUDA_TRY(cudaStreamWaitEvent(copy_stream_, ev_strip_[k], 0));
-          if (copy_bands(rb_host_, a.dst_addr, a.dst_width, a.dst_height, b0, k + 1 == S ? my_bands + 1 : b1, copy_stream_) != 0) return -1;
+          if (copy_bands(rb_host_, a.dst_addr, a.dst_width, a.dst_height, b0, b1 == my_bands ? my_bands + 1 : b1, copy_stream_) != 0) return -1;
         }
         if (rc >= 0) {   // the main stream joins the other two: kernel time ends where the last strip ends, the run where the last copy ends
           for (uint32_t k = 0; k < S; k++) CUDA_TRY(cudaStreamWaitEvent(stream_, ev_strip_[k], 0));
@@ -1465,9 +1486,10 @@ private:
   static constexpr uint32_t kStrips = 8, kMaxStrips = 16;
   uint64_t rb_addr_ = 0, rb_bytes_ = 0;
   uint8_t *rb_host_ = nullptr;
-  bool rb_issued_ = false, kend_valid_ = false;
+  bool rb_issued_ = false, kend_valid_ = false, half_valid_ = false, strip_reverse_ = false;
+  float strip_half_share_ = 0.5f;
   cudaStream_t aux_stream_ = nullptr, copy_stream_ = nullptr;
-  cudaEvent_t ev_strip_[kMaxStrips + 1] = {}, ev_kend_ = nullptr;
+  cudaEvent_t ev_strip_[kMaxStrips + 1] = {}, ev_kend_ = nullptr, ev_half_ = nullptr;
   uint32_t *strip_counters_ = nullptr;
   int strips_init_locked() {
     if (aux_stream_) return 0;
@@ -1475,6 +1497,7 @@ private:
     CUDA_TRY(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
     for (auto &e : ev_strip_) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CUDA_TRY(cudaEventCreate(&ev_kend_));
+    CUDA_TRY(cudaEventCreate(&ev_half_));
     CUDA_TRY(cudaMalloc(&strip_counters_, sizeof(uint32_t) * kMaxStrips));
     return 0;
   }
@@ -1482,9 +1505,9 @@ private:
     if (!aux_stream_) return;
     cudaStreamDestroy(aux_stream_), cudaStreamDestroy(copy_stream_);
     for (auto &e : ev_strip_) cudaEventDestroy(e), e = nullptr;
-    cudaEventDestroy(ev_kend_);
+    cudaEventDestroy(ev_kend_), cudaEventDestroy(ev_half_);
     cudaFree(strip_counters_);
-    aux_stream_ = copy_stream_ = nullptr, ev_kend_ = nullptr, strip_counters_ = nullptr;
+    aux_stream_ = copy_stream_ = nullptr, ev_kend_ = ev_half_ = nullptr, strip_counters_ = nullptr;
   }
   uint8_t *stage_ = nullptr;           // page-locked ring for small uploads
   cudaEvent_t stage_ev_[kStageSlots] = {};
