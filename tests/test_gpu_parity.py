@@ -471,3 +471,46 @@ def test_readback_strips_deliver_the_same_frame():
         os.environ.pop("VORTEX_B200_SCHEDULE", None)
         os.environ.pop("VORTEX_B200_READBACK_MIN_TILES", None)
         tr.close()
+
+
+def test_readback_strip_order_with_a_band_partition():
+    """The strips may go top-down or bottom-up (VORTEX_B200_READBACK_ORDER; by default the previous frame's timing decides) and may
+    be tapered; with a band partition (what every GPU of a group has) a rank's strips must deliver exactly that rank's bands —
+    including the short last band — and touch nothing else of the host image."""
+    import torch
+    port = po.PortRaycast() if po.have_port() else best_oracle()
+    sc = port.scene_create([scenes.heightfield(224)])
+    w, h = 2048, 1100                                   # 137 bands of 8 rows + 4 rows
+    karg = sc.setup(w, h)
+    tr = tracer_for(sc, karg)
+    os.environ["VORTEX_B200_SCHEDULE"] = "0"
+    os.environ["VORTEX_B200_READBACK_MIN_TILES"] = "1000"
+    keys = ("VORTEX_B200_READBACK_STRIPS", "VORTEX_B200_READBACK_TAPER", "VORTEX_B200_READBACK_ORDER")
+    try:
+        tr.set_mode(1, 0)
+        want = tr.run().copy()
+        host = torch.zeros((h, w), dtype=torch.int32).pin_memory()
+        tr.dev.set_readback(tr.out, host.data_ptr(), w * h * 4)
+        band_of_row = np.arange(h) // 8
+        for world in (2, 3, 1):
+            for rank in range(world):
+                tr.dev.set_partition(rank, world, 8)
+                mine = (band_of_row % world) == rank
+                for strips, taper, order in (("4", "100", "1"), ("5", "80", "1"), ("5", "80", "0"), ("4", "100", "2")):
+                    for k, v in zip(keys, (strips, taper, order)):
+                        os.environ[k] = v
+                    for frame in range(3 if order == "2" else 1):
+                        host.zero_()
+                        tr.dev.start(tr.krnl, tr.args)
+                        tr.dev.ready_wait()
+                        got = host.numpy().view(np.uint32)
+                        assert np.array_equal(got[mine], want[mine]), (world, rank, strips, taper, order, frame)
+                        assert not got[~mine].any(), (world, rank, strips, taper, order, frame)
+                        st = tr.dev.stats()
+                        assert st["kernel_launches"] - st["prep_launches"] == int(strips), (strips, st)
+        tr.dev.set_partition(0, 1, 8)
+        tr.dev.set_readback(tr.out, None, 0)
+    finally:
+        for k in keys + ("VORTEX_B200_SCHEDULE", "VORTEX_B200_READBACK_MIN_TILES"):
+            os.environ.pop(k, None)
+        tr.close()
